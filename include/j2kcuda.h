@@ -1,0 +1,208 @@
+/*
+ * j2kcuda.h -- C ABI of libj2kcuda, the B200-native JPEG 2000 codec core.
+ *
+ * Drop-in boundary: everything the reference's plug-in layer reaches through the abstract
+ * j2k::Codec (src/common/j2k_codec.h:279-326) and that its only registered implementation,
+ * OpenJPEGCodec (src/common/j2k_openjpeg_codec.cpp:213-758), forwards to the opj_* C API
+ * (ext/grok/src/lib/openjp2/openjpeg.h).  Plain C types only: no exceptions, no torch types,
+ * caller-owned pixel memory, library-owned output freed by j2kcuda_free().
+ *
+ * There is NO CPU fallback: every pixel-path entry point returns J2KCUDA_ERR_NO_DEVICE when no
+ * sm_100 device is usable.  Tier-2 (packets, PCRD, markers) runs on the host by design, as in
+ * the reference's accelerator hand-off (ext/grok/src/lib/openjp2/plugin_bridge.cpp:72-174).
+ */
+#ifndef J2KCUDA_H
+#define J2KCUDA_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define J2KCUDA_VERSION 0x000100
+
+enum {
+    J2KCUDA_OK = 0,
+    J2KCUDA_ERR_PARAM = 1,      /* bad argument (what OpenJPEGCodec would throw Exception for) */
+    J2KCUDA_ERR_NO_DEVICE = 2,  /* no CUDA device / kernels unavailable: never falls back */
+    J2KCUDA_ERR_CUDA = 3,       /* a CUDA call failed; see j2kcuda_last_error() */
+    J2KCUDA_ERR_STREAM = 4,     /* malformed / unsupported codestream */
+    J2KCUDA_ERR_NOMEM = 5,
+    J2KCUDA_ERR_ABORTED = 6,    /* abort callback returned non-zero */
+    J2KCUDA_ERR_UNSUPPORTED = 7
+};
+
+/* j2k::SampleType, src/common/j2k_codec.h:212-219 */
+enum { J2KCUDA_UCHAR = 0, J2KCUDA_USHORT = 1, J2KCUDA_UINT = 2, J2KCUDA_INT = 3 };
+
+/* One channel of pixels in caller memory; same fields as j2k::Channel
+ * (src/common/j2k_codec.h:221-247).  From After Effects the four channels alias one interleaved
+ * ARGB world (buf = base + i*sample, colbytes = 4*sample; src/aftereffects/j2k.cpp:324-362). */
+typedef struct j2kcuda_plane {
+    void*    buf;
+    int64_t  colbytes;     /* bytes between horizontally adjacent samples */
+    int64_t  rowbytes;     /* bytes between rows */
+    uint32_t width, height;
+    uint8_t  sample_type;  /* J2KCUDA_UCHAR ... */
+    uint8_t  depth;        /* significant bits in the caller's samples */
+    uint8_t  sgnd;
+    uint8_t  reserved;
+} j2kcuda_plane;
+
+/* OPJ_PROG_ORDER, ext/grok/src/lib/openjp2/openjpeg.h:303-310 */
+enum { J2KCUDA_LRCP = 0, J2KCUDA_RLCP = 1, J2KCUDA_RPCL = 2, J2KCUDA_PCRL = 3, J2KCUDA_CPRL = 4 };
+/* rsiz profiles, openjpeg.h:225-226 */
+enum { J2KCUDA_PROFILE_NONE = 0, J2KCUDA_PROFILE_CINEMA_2K = 3, J2KCUDA_PROFILE_CINEMA_4K = 4 };
+/* Which encoder's Tier-2 policy to reproduce byte for byte. */
+enum { J2KCUDA_COMPAT_GROK_2_1_1 = 0, J2KCUDA_COMPAT_OPENJPEG_2_5 = 1 };
+
+/* Encoder parameters: the subset of opj_cparameters_t (openjpeg.h:356-486) the plug-in and the
+ * BASELINE configs use; zero means "library default" (openjpeg.cpp:706-728). */
+typedef struct j2kcuda_params {
+    uint32_t width, height;      /* image size (x0 = y0 = 0 as the plug-in always sets) */
+    uint32_t ncomp;              /* 1..4 */
+    uint32_t prec;               /* bits per sample in the codestream, 1..16 */
+    uint32_t sgnd;
+    uint32_t irreversible;       /* 0: 5/3 + RCT, 1: 9/7 + ICT */
+    uint32_t numresolution;      /* 0 -> 6 */
+    uint32_t cblk_w, cblk_h;     /* 0 -> 64 */
+    uint32_t mct;                /* tcp_mct: 0 none, 1 RCT/ICT on components 0..2 */
+    uint32_t prog_order;         /* J2KCUDA_LRCP ... */
+    uint32_t tile_w, tile_h;     /* 0 -> single tile */
+    uint32_t numlayers;          /* 0 -> 1 */
+    uint32_t profile;            /* J2KCUDA_PROFILE_* */
+    uint32_t max_comp_size;      /* cinema: bytes per component per frame; 0 -> profile default */
+    uint64_t max_cs_size;        /* cinema: bytes per frame; 0 -> profile default */
+    double   rates[16];          /* tcp_rates: compression ratio per layer, 0 = lossless */
+    uint32_t compat;             /* J2KCUDA_COMPAT_* */
+    int32_t  device;             /* CUDA ordinal, -1 = current */
+    uint32_t reserved[6];
+} j2kcuda_params;
+
+/* What GetFileInfo needs from the main header (j2k_openjpeg_codec.cpp:222-429). */
+typedef struct j2kcuda_info {
+    uint32_t width, height, ncomp;
+    uint32_t prec[4], sgnd[4], dx[4], dy[4];
+    uint32_t reversible, numresolution, numlayers, mct, prog_order;
+    uint32_t tile_w, tile_h, tiles_x, tiles_y;
+    uint32_t cblk_w, cblk_h, profile;
+    uint32_t is_jp2;             /* input was a JP2 box file; codestream located inside */
+    uint64_t codestream_offset, codestream_length;
+} j2kcuda_info;
+
+typedef int  (*j2kcuda_abort_fn)(void* user);                 /* non-zero = stop */
+typedef void (*j2kcuda_log_fn)(void* user, int level, const char* msg);
+
+/* ---- lifetime ------------------------------------------------------------------------------ */
+int  j2kcuda_init(int device, j2kcuda_log_fn log, void* user);     /* replaces opj_initialize */
+void j2kcuda_shutdown(void);
+int  j2kcuda_version(void);
+int  j2kcuda_device_count(void);
+const char* j2kcuda_last_error(void);                               /* thread-local */
+void j2kcuda_free(void* p);
+void j2kcuda_default_params(j2kcuda_params* p);     /* opj_set_default_encoder_parameters */
+
+/* ---- the reference-facing calls ------------------------------------------------------------ */
+/* replaces opj_read_header(_ex) as used by OpenJPEGCodec::GetFileInfo */
+int j2kcuda_probe(const uint8_t* bytes, size_t n, j2kcuda_info* out);
+/* replaces opj_setup_encoder + opj_start_compress + opj_encode + opj_end_compress
+ * (j2k_openjpeg_codec.cpp:722-736).  planes[c] live in HOST memory.  *out is malloc'd. */
+int j2kcuda_encode(const j2kcuda_params* p, const j2kcuda_plane* planes, int nplanes,
+                   uint8_t** out, size_t* out_len);
+/* replaces opj_read_header + opj_decode (j2k_openjpeg_codec.cpp:489-512) and the CopyBuffer that
+ * follows (:528-562).  reduce = log2(subsample).  planes[c] are HOST destinations sized
+ * ceil(w / 2^reduce) x ceil(h / 2^reduce). */
+int j2kcuda_decode(const uint8_t* bytes, size_t n, unsigned reduce, const j2kcuda_plane* planes,
+                   int nplanes, j2kcuda_abort_fn abort_fn, void* user);
+
+/* ---- persistent contexts (image sequences: configs C4/C5; also what bench.py times) -------- */
+typedef struct j2kcuda_encoder j2kcuda_encoder;
+typedef struct j2kcuda_decoder j2kcuda_decoder;
+
+j2kcuda_encoder* j2kcuda_encoder_create(const j2kcuda_params* p);
+void j2kcuda_encoder_destroy(j2kcuda_encoder* e);
+/* host planes -> device staging (async on the context's stream) */
+int j2kcuda_encoder_upload(j2kcuda_encoder* e, const j2kcuda_plane* planes, int nplanes);
+/* pixels already resident on the device: interleaved samples, `ncomp` per pixel,
+ * sample_type UCHAR/USHORT, pitch in bytes */
+int j2kcuda_encoder_set_device_input(j2kcuda_encoder* e, const void* d_pixels, int64_t pitch_bytes,
+                                     int sample_type);
+/* device stages (MCT, DWT, T1) for all tiles + D2H of code-block bytes / pass tables */
+int j2kcuda_encoder_run(j2kcuda_encoder* e);
+/* host Tier-2: PCRD, packets, markers -> codestream (malloc'd) */
+int j2kcuda_encoder_finish(j2kcuda_encoder* e, uint8_t** out, size_t* out_len);
+/* per-stage device times of the last run, milliseconds (CUDA events on the context's stream):
+ * [0] upload  [1] mct  [2] dwt  [3] t1 context  [4] t1 mq  [5] compact + D2H  [6] host tier-2 (wall)
+ * [7] dwt level-1 launch only.  Returns number of entries written. */
+int j2kcuda_encoder_timings(j2kcuda_encoder* e, float* ms, int n);
+/* counters of the last run: [0] kernels launched [1] code-blocks [2] MQ symbols
+ * [3] compressed bytes [4] h2d bytes [5] d2h bytes */
+int j2kcuda_encoder_counters(j2kcuda_encoder* e, uint64_t* v, int n);
+
+j2kcuda_decoder* j2kcuda_decoder_create(int device);
+void j2kcuda_decoder_destroy(j2kcuda_decoder* d);
+/* host Tier-2 parse + H2D of code-block segments */
+int j2kcuda_decoder_prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned reduce);
+/* device stages: T1 decode, dequantise, inverse DWT, inverse MCT, level shift, clamp */
+int j2kcuda_decoder_run(j2kcuda_decoder* d);
+/* device -> host planes */
+int j2kcuda_decoder_download(j2kcuda_decoder* d, const j2kcuda_plane* planes, int nplanes);
+/* keep result on device: interleaved u8/u16, `ncomp` samples per pixel */
+int j2kcuda_decoder_get_device_output(j2kcuda_decoder* d, void** d_pixels, int64_t* pitch_bytes,
+                                      int* sample_type);
+/* [0] host tier-2 parse (wall) [1] H2D [2] t1 [3] idwt [4] imct+pack [5] D2H [6] idwt finest level */
+int j2kcuda_decoder_timings(j2kcuda_decoder* d, float* ms, int n);
+int j2kcuda_decoder_counters(j2kcuda_decoder* d, uint64_t* v, int n);
+
+/* ---- batches: frames of a sequence on this process's device (one process per GPU) --------- */
+int j2kcuda_encode_batch(const j2kcuda_params* p, const j2kcuda_plane* const* frames, int nframes,
+                         int nplanes, uint8_t** outs, size_t* out_lens);
+int j2kcuda_decode_batch(const uint8_t* const* streams, const size_t* lens, int nframes,
+                         unsigned reduce, const j2kcuda_plane* const* frames, int nplanes);
+
+/* ---- stage entry points (host arrays in/out; what the parity tests drive, one stage at a
+ *      time, the way ext/grok's OPJ_PLUGIN_STATE_DEBUG_ENCODE cross-check does) -------------- */
+/* RCT / ICT on three int32 planes (inverse ICT: float32 bit patterns). mct.cpp:94-471 */
+int j2kcuda_stage_mct(int32_t* c0, int32_t* c1, int32_t* c2, size_t n, int irreversible, int inverse);
+/* multi-level DWT of one tile-component, Mallat layout in and out. dwt.cpp:420-506, 615-704,
+ * 927-1062.  (x0,y0,x1,y1) = canvas bounds of the tile-component. */
+int j2kcuda_stage_dwt(int32_t* data, int x0, int y0, int x1, int y1, int numres, int irreversible,
+                      int inverse);
+/* Quantise + tier-1 encode `nblk` code-blocks cut from one plane.  blk[i] = {x, y, w, h, orient,
+ * bandconst}; 5/3 when irreversible == 0.  Outputs per block: numbps, npasses, cumulative rates
+ * (stride 128), per-pass nmsedec (stride 128), bytes at data + offsets[i]. t1_opt.cpp:659-739 */
+int j2kcuda_stage_t1_encode(const int32_t* plane, int stride, int height, const int32_t* blk,
+                            int nblk, int irreversible, int32_t* numbps, int32_t* npasses,
+                            int32_t* rates, int32_t* nmsedec, uint8_t* data, size_t data_cap,
+                            uint64_t* offsets);
+/* Tier-1 decode: blk[i] = {w, h, orient, numbps, npasses, len}; bytes concatenated in `data`.
+ * out = concatenated w*h int32 per block in the reference decoder's representation
+ * (t1.cpp:1337-1448: magnitude with one extra fractional bit). */
+int j2kcuda_stage_t1_decode(const uint8_t* data, const int32_t* blk, int nblk, int32_t* out);
+
+/* Host Tier-2 alone, from externally supplied code-block results (the grok plug-in hand-off,
+ * plugin_bridge.cpp:72-174): blocks in tile -> component -> resolution -> band -> precinct ->
+ * code-block order.  rates are raw cumulative `mqc_numbytes + 3` values already clamped and
+ * 0xFF-trimmed (t1_opt.cpp:722-736); dist are cumulative distortion decreases. */
+typedef struct j2kcuda_block_result {
+    const uint8_t* data;
+    int32_t numbps, npasses;
+    const int32_t* rates;
+    const double* dist;
+} j2kcuda_block_result;
+int j2kcuda_t2_block_count(const j2kcuda_params* p);
+/* Geometry of every code-block in that order, 12 int32 per block: tile, comp, x, y (position in the
+ * tile-component's Mallat plane), w, h, orient, level (numres-1-resno), band numbps, bandconst
+ * (t1.cpp:1482), band stepsize (float32 bits), resno.  Returns blocks written.  (tcd.cpp:592-842) */
+int j2kcuda_t2_block_geometry(const j2kcuda_params* p, int32_t* geo, int max_blocks);
+int j2kcuda_t2_assemble(const j2kcuda_params* p, const j2kcuda_block_result* blocks, int nblocks,
+                        uint8_t** out, size_t* out_len);
+/* Host Tier-2 parse alone: returns, per code-block in the same order, numbps, npasses, len and
+ * offset of its (concatenated) bytes inside `bytes`-derived scratch returned in *seg (malloc'd). */
+int j2kcuda_t2_parse(const uint8_t* bytes, size_t n, unsigned reduce, int32_t** blkinfo,
+                     int* nblocks, uint8_t** seg, size_t* seg_len);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,91 @@
+// C-ABI entry points that are host-only: parameter defaults, Tier-2 assembly from externally
+// supplied block results (the grok plug-in hand-off), Tier-2 parse, probe.  See include/j2kcuda.h.
+#include "../../include/j2kcuda.h"
+#include "t2.h"
+#include "common.h"
+#include <cstdlib>
+#include <cstring>
+
+using namespace j2k;
+
+extern "C" {
+
+int j2kcuda_version(void) { return J2KCUDA_VERSION; }
+const char* j2kcuda_last_error(void) { return j2k::last_error().c_str(); }
+void j2kcuda_free(void* p) { free(p); }
+
+void j2kcuda_default_params(j2kcuda_params* p) {   // openjpeg.cpp:706-728
+    if (!p) return;
+    memset(p, 0, sizeof(*p));
+    p->numresolution = 6;
+    p->cblk_w = p->cblk_h = 64;
+    p->prog_order = J2KCUDA_LRCP;
+    p->numlayers = 1;
+    p->device = -1;
+}
+
+int j2kcuda_t2_block_count(const j2kcuda_params* p) {
+    if (!p) return -1;
+    CodingParams cp;
+    setup_coding_params(*p, cp);
+    int n = 0;
+    for (int t = 0; t < (int)(cp.tw * cp.th); ++t) {
+        TileGeo g;
+        build_tile(cp, t, 1.0f, g);
+        n += (int)g.cblks.size();
+    }
+    return n;
+}
+
+int j2kcuda_t2_block_geometry(const j2kcuda_params* p, int32_t* geo, int max_blocks) {
+    if (!p || !geo) return -1;
+    CodingParams cp;
+    setup_coding_params(*p, cp);
+    int n = 0;
+    for (int t = 0; t < (int)(cp.tw * cp.th); ++t) {
+        TileGeo g;
+        build_tile(cp, t, 1.0f, g);
+        for (auto& cb : g.cblks) {
+            if (n >= max_blocks) return n;
+            const BandGeo& band = g.comps[cb.comp].res[cb.res].bands[cb.band];
+            int32_t* o = geo + 12 * (size_t)n;
+            o[0] = t; o[1] = cb.comp; o[2] = cb.px; o[3] = cb.py; o[4] = cb.r.w(); o[5] = cb.r.h();
+            o[6] = cb.orient; o[7] = cp.comps[cb.comp].numres - 1 - cb.res; o[8] = band.numbps;
+            o[9] = band_const(band.stepsize);
+            memcpy(&o[10], &band.stepsize, 4);
+            o[11] = cb.res;
+            ++n;
+        }
+    }
+    return n;
+}
+
+int j2kcuda_t2_assemble(const j2kcuda_params* p, const j2kcuda_block_result* blocks, int nblocks,
+                        uint8_t** out, size_t* out_len) {
+    if (!p || !blocks || !out || !out_len) return set_error(J2KCUDA_ERR_PARAM, "null argument");
+    EncoderHost host;
+    setup_coding_params(*p, host.cp);
+    int nt = (int)(host.cp.tw * host.cp.th);
+    std::vector<EncTile> tiles(nt);
+    int k = 0;
+    for (int t = 0; t < nt; ++t) {
+        init_enc_tile(host.cp, t, tiles[t]);
+        for (auto& b : tiles[t].blocks) {
+            if (k >= nblocks) return set_error(J2KCUDA_ERR_PARAM, "too few block results");
+            b.data = blocks[k].data; b.numbps = blocks[k].numbps; b.totalpasses = blocks[k].npasses;
+            b.rates = blocks[k].rates; b.dist = blocks[k].dist;
+            ++k;
+        }
+    }
+    if (k != nblocks) return set_error(J2KCUDA_ERR_PARAM, "block count mismatch");
+    std::vector<uint8_t> cs;
+    std::string err;
+    if (!host.assemble(tiles, cs, err)) return set_error(J2KCUDA_ERR_PARAM, err);
+    *out = (uint8_t*)malloc(cs.size() ? cs.size() : 1);
+    if (!*out) return set_error(J2KCUDA_ERR_NOMEM, "malloc");
+    memcpy(*out, cs.data(), cs.size());
+    *out_len = cs.size();
+    return J2KCUDA_OK;
+}
+
+}  // extern "C"
