@@ -1,0 +1,566 @@
+// EBCOT Tier-1 encoder for sm_100a, split in two kernels.
+//
+//  k_t1_context  one code-block per warp.  Quantises the block (T1Encoder.cpp:103-174), keeps the
+//                significance / sign / visited / refined state of its up-to-64 rows as 64-bit row
+//                masks (bit x = column x) built with __ballot_sync, and produces the exact sequence
+//                of (context, decision) pairs the reference's three coding passes would feed to the
+//                MQ coder (t1_opt.cpp:330-576), plus the per-pass distortion estimates
+//                (t1.cpp:298-314).  Only the significance-propagation pass has a true scan-order
+//                dependency; it is resolved as a monotone fix-point on the row masks (lane = stripe,
+//                neighbour stripes exchanged with warp shuffles).  Given the membership, every
+//                sample's context depends only on masks "before" and "after" the pass, so the 32
+//                lanes emit disjoint (stripe, column-range) pieces of the pass in parallel at
+//                offsets obtained from popcounts and a warp prefix sum.
+//  k_t1_mq       one code-block per thread: the MQ arithmetic coder proper (mqc.cpp:223-452) with
+//                A, C, CT and the pending byte in registers, consuming the symbol stream and
+//                recording the byte count after every pass (t1_opt.cpp:711-736).
+//
+// Scan order (t1_opt.cpp:384-400): stripes of four rows, columns left to right inside a stripe, rows
+// top to bottom inside a column.
+#include "device.h"
+#include "t1_tables.cuh"
+
+namespace j2k {
+namespace {
+
+typedef unsigned long long u64;
+constexpr int CX_WARPS = 4;
+constexpr unsigned FULL = 0xffffffffu;
+
+struct Rows {                 // index = row + 1; entries 0 and 65 stay zero
+    u64 sgn[66], sig[66], bit[66], mem[66], nsp[66], ref[66];
+};
+struct Luts {
+    uint8_t zc[4 * 256];
+    uint8_t sc[256];
+    int16_t nm_sig[128], nm_sig0[128], nm_ref[128], nm_ref0[128];
+};
+
+__device__ __forceinline__ int fix_mul_t1(int a, int b) {      // opj_intmath.h:268-279
+    return (int)(((long long)a * (long long)b + 4096) >> 18);
+}
+
+// sign-magnitude sample: bit 31 sign, 6 fractional bits (T1Encoder.cpp:139-171, t1_opt.h:169)
+__device__ __forceinline__ uint32_t load_smag(const T1Block& b, int x, int y) {
+    int v = __ldg(b.coeff + (size_t)y * b.pitch + x);
+    int t = b.qmfbid ? v * 64 : fix_mul_t1(v, b.bandconst);
+    uint32_t mag = (uint32_t)(t < 0 ? -t : t);
+    return mag | (t < 0 ? 0x80000000u : 0u);
+}
+
+__device__ __forceinline__ int nmsedec_sig(const Luts& L, uint32_t mag, int bpno) {
+    return bpno > 0 ? L.nm_sig[(mag >> bpno) & 127] : L.nm_sig0[mag & 127];
+}
+__device__ __forceinline__ int nmsedec_ref(const Luts& L, uint32_t mag, int bpno) {
+    return bpno > 0 ? L.nm_ref[(mag >> bpno) & 127] : L.nm_ref0[mag & 127];
+}
+
+// Byte-stream writer of one lane: symbols go out as aligned 32-bit words where the lane owns the
+// whole word, as single bytes at the ragged ends it shares with its neighbours.
+struct Emitter {
+    uint8_t* base;
+    uint32_t first, pos, acc;
+    __device__ void init(uint8_t* b, uint32_t start) { base = b; first = pos = start; acc = 0; }
+    __device__ __forceinline__ void push(uint32_t ctx, uint32_t d) {
+        acc |= ((ctx << 1) | d) << ((pos & 3) * 8);
+        ++pos;
+        if ((pos & 3) == 0) flush_word();
+    }
+    __device__ void flush_word() {
+        uint32_t w0 = pos - 4;
+        if (w0 >= first) *reinterpret_cast<uint32_t*>(base + w0) = acc;
+        else for (uint32_t p = first; p < pos; ++p) base[p] = (uint8_t)(acc >> ((p & 3) * 8));
+        acc = 0;
+    }
+    __device__ void finish() {
+        uint32_t w0 = pos & ~3u;
+        for (uint32_t p = (w0 > first ? w0 : first); p < pos; ++p) base[p] = (uint8_t)(acc >> ((p & 3) * 8));
+    }
+};
+
+enum { PASS_SIG = 0, PASS_REF = 1, PASS_CLN = 2 };
+
+__device__ __forceinline__ u64 win(u64 m, int c0) { return c0 ? (m >> (c0 - 1)) : (m << 1); }
+__device__ __forceinline__ uint32_t w3(u64 m, int j) {          // bits j..j+2 of a windowed row, j <= 31
+    return __funnelshift_r((uint32_t)m, (uint32_t)(m >> 32), j) & 7u;
+}
+
+// Emit one coding pass of one block.  Returns the number of symbols of the pass (warp-uniform).
+// `sym` points at the block's symbol slot, `done` symbols are already there.
+template <int PASS>
+__device__ uint32_t emit_pass(const Rows& R, const Luts& L, const T1Block& blk, int lane, uint8_t* sym,
+                              uint32_t done, uint32_t cap, bool& overflow) {
+    const int w = blk.w, h = blk.h;
+    const int nstripes = (h + 3) >> 2;
+    int p2 = 1;
+    while (p2 < nstripes) p2 <<= 1;
+    const int lps = 32 / p2;                       // lanes per stripe
+    const int segw = (w + lps - 1) / lps;          // <= 32
+    const int stripe = lane / lps, seg = lane % lps;
+    const int c0 = seg * segw;
+    int ncols = min(segw, w - c0);
+    if (stripe >= nstripes || ncols < 0) ncols = 0;
+    const u64 colmask = w == 64 ? ~0ull : ((1ull << w) - 1);
+    const uint32_t lmask = ncols >= 32 ? 0xffffffffu : ((1u << ncols) - 1u);
+    const uint8_t* zc = L.zc + blk.orient * 256;
+
+    // rows q = 0..5 <-> y = 4*stripe - 1 + q ; windowed so that local column j sits at bit j+1
+    u64 A[6], B[6], SG[6];
+    uint32_t MB[4], BT[4], RF[4];
+    const int ybase = 4 * (stripe < nstripes ? stripe : 0);
+#pragma unroll
+    for (int q = 0; q < 6; ++q) {
+        const int i = ybase + q;                   // = y + 1
+        const u64 s0 = R.sig[i], np = R.nsp[i], mm = R.mem[i], bt = R.bit[i];
+        const u64 valid = (i >= 1 && i <= h) ? colmask : 0ull;
+        u64 a, b, memb;
+        if (PASS == PASS_SIG) { b = s0; a = s0 | np; memb = mm; }
+        else if (PASS == PASS_REF) { a = b = s0 | np; memb = s0; }
+        else { b = s0 | np; memb = ~(b | mm) & valid; a = b | (memb & bt); }
+        A[q] = win(a, c0); B[q] = win(b, c0); SG[q] = win(R.sgn[i], c0);
+        if (q >= 1 && q <= 4) {
+            MB[q - 1] = (uint32_t)(memb >> c0) & lmask;
+            BT[q - 1] = (uint32_t)(bt >> c0) & lmask;
+            RF[q - 1] = (uint32_t)(R.ref[i] >> c0) & lmask;
+        }
+    }
+    uint32_t AG = 0;                               // run-length (aggregation) columns, t1_opt.cpp:487-515
+    if (PASS == PASS_CLN) {
+        // a column is coded in run-length mode when its four samples are all still to be coded
+        // and nothing in its 3x6 neighbourhood is significant at the time the column is reached:
+        // row above and left column in their state after this pass, right column and row below
+        // in their state before it
+        u64 up, left = 0, right = 0, own = 0, down, memall = ~0ull;
+        {
+            const int i0 = ybase, i5 = ybase + 5;
+            const u64 b0 = R.sig[i0] | R.nsp[i0];
+            const u64 valid0 = (i0 >= 1 && i0 <= h) ? colmask : 0ull;
+            const u64 a0 = b0 | (~(b0 | R.mem[i0]) & valid0 & R.bit[i0]);
+            up = (a0 << 1) | a0 | (a0 >> 1);
+            const u64 b5 = R.sig[i5] | R.nsp[i5];
+            down = (b5 << 1) | b5 | (b5 >> 1);
+        }
+#pragma unroll
+        for (int q = 1; q <= 4; ++q) {
+            const int i = ybase + q;
+            const u64 b = R.sig[i] | R.nsp[i];
+            const u64 valid = (i >= 1 && i <= h) ? colmask : 0ull;
+            const u64 memb = ~(b | R.mem[i]) & valid;
+            const u64 a = b | (memb & R.bit[i]);
+            left |= a << 1; right |= b >> 1; own |= b; memall &= memb;
+        }
+        const bool fullstripe = ybase + 3 < h;
+        u64 agg = fullstripe ? (~(up | left | right | own | down) & memall) : 0ull;
+        AG = (uint32_t)(agg >> c0) & lmask;
+    }
+
+    // ---- count ----
+    uint32_t cnt = 0;
+    if (PASS == PASS_SIG) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) cnt += __popc(MB[r]) + __popc(MB[r] & BT[r]);
+    } else if (PASS == PASS_REF) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) cnt += __popc(MB[r]);
+    } else {
+        const uint32_t NA = ~AG;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) cnt += __popc(MB[r] & NA) + __popc(MB[r] & NA & BT[r]);
+        const uint32_t f0 = AG & BT[0], f1 = AG & ~BT[0] & BT[1], f2 = AG & ~BT[0] & ~BT[1] & BT[2];
+        const uint32_t f3 = AG & ~BT[0] & ~BT[1] & ~BT[2] & BT[3];
+        const uint32_t fz = AG & ~(BT[0] | BT[1] | BT[2] | BT[3]);
+        cnt += __popc(fz);                                           // AGG 0
+        cnt += 4 * (__popc(f0) + __popc(f1) + __popc(f2) + __popc(f3));   // AGG 1, two UNI, sign
+        cnt += 3 * __popc(f0) + 2 * __popc(f1) + __popc(f2);         // zero coding of the rows below
+        cnt += __popc(f0 & BT[1]) + __popc(f0 & BT[2]) + __popc(f0 & BT[3]);   // their signs
+        cnt += __popc(f1 & BT[2]) + __popc(f1 & BT[3]) + __popc(f2 & BT[3]);
+    }
+    if (ncols == 0) cnt = 0;
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t t = __shfl_up_sync(FULL, incl, d);
+        if (lane >= d) incl += t;
+    }
+    const uint32_t total = __shfl_sync(FULL, incl, 31);
+    if (done + total > cap) { overflow = true; return total; }
+    if (cnt == 0) return total;
+
+    Emitter E;
+    E.init(sym, done + incl - cnt);
+    uint32_t cols = MB[0] | MB[1] | MB[2] | MB[3];
+    while (cols) {
+        const int j = __ffs(cols) - 1;
+        cols &= cols - 1;
+        uint32_t wa[6], wb[6], ws[6];
+#pragma unroll
+        for (int q = 0; q < 6; ++q) { wa[q] = w3(A[q], j); wb[q] = w3(B[q], j); ws[q] = w3(SG[q], j); }
+        int rstart = 0;
+        bool pending_sign = false;
+        if (PASS == PASS_CLN && ((AG >> j) & 1)) {
+            const uint32_t bb = ((BT[0] >> j) & 1) | (((BT[1] >> j) & 1) << 1) | (((BT[2] >> j) & 1) << 2) | (((BT[3] >> j) & 1) << 3);
+            if (bb == 0) { E.push(CTX_AGG, 0); continue; }
+            const int r0 = __ffs(bb) - 1;
+            E.push(CTX_AGG, 1);
+            E.push(CTX_UNI, (uint32_t)r0 >> 1);
+            E.push(CTX_UNI, (uint32_t)r0 & 1);
+            rstart = r0;
+            pending_sign = true;
+        }
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            if (r < rstart || !((MB[r] >> j) & 1)) continue;
+            const int q = r + 1;
+            const uint32_t bit = (BT[r] >> j) & 1;
+            if (PASS == PASS_REF) {
+                const uint32_t nb = wa[q - 1] | (wa[q] & 5u) | wa[q + 1];
+                const uint32_t ctx = ((RF[r] >> j) & 1) ? CTX_MAG + 2 : (nb ? CTX_MAG + 1 : CTX_MAG);
+                E.push(ctx, bit);
+                continue;
+            }
+            if (!(pending_sign && r == rstart)) {
+                const uint32_t above = r == 0 ? wa[0] : ((wa[q - 1] & 3u) | (wb[q - 1] & 4u));
+                const uint32_t below = r == 3 ? wb[5] : ((wa[q + 1] & 1u) | (wb[q + 1] & 6u));
+                const uint32_t nb = above | ((wa[q] & 1u) << 3) | (((wb[q] >> 2) & 1u) << 4) | (below << 5);
+                E.push(zc[nb], bit);
+            }
+            if (bit) {
+                const uint32_t sw = wa[q] & 1u, se = (wb[q] >> 2) & 1u;
+                const uint32_t sn = (wa[q - 1] >> 1) & 1u, ss = (wb[q + 1] >> 1) & 1u;
+                const uint32_t idx = sw | (se << 1) | (sn << 2) | (ss << 3) |
+                                     ((sw & ws[q]) << 4) | ((se & (ws[q] >> 2)) << 5) |
+                                     ((sn & (ws[q - 1] >> 1)) << 6) | ((ss & (ws[q + 1] >> 1)) << 7);
+                const uint32_t e = L.sc[idx];
+                E.push(CTX_SC + (e & 7u), ((ws[q] >> 1) & 1u) ^ (e >> 3));
+            }
+        }
+    }
+    E.finish();
+    return total;
+}
+
+__global__ void __launch_bounds__(32 * CX_WARPS)
+k_t1_context(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __restrict__ tab,
+             uint8_t* __restrict__ sym_arena, uint32_t* __restrict__ pass_nsym, T1Result* __restrict__ results) {
+    __shared__ Rows s_rows[CX_WARPS];
+    __shared__ Luts L;
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) L.zc[i] = tab->zc[i];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) L.sc[i] = tab->sc[i];
+    for (int i = threadIdx.x; i < 128; i += blockDim.x) {
+        L.nm_sig[i] = tab->nm_sig[i]; L.nm_sig0[i] = tab->nm_sig0[i];
+        L.nm_ref[i] = tab->nm_ref[i]; L.nm_ref0[i] = tab->nm_ref0[i];
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int bi = blockIdx.x * CX_WARPS + warp;
+    if (bi >= nblocks) return;
+    const T1Block blk = blocks[bi];
+    Rows& R = s_rows[warp];
+    T1Result& res = results[bi];
+    const int w = blk.w, h = blk.h;
+    {
+        u64* z = reinterpret_cast<u64*>(&R);
+        for (int i = lane; i < (int)(sizeof(Rows) / sizeof(u64)); i += 32) z[i] = 0;
+    }
+    __syncwarp();
+    const bool c0ok = lane < w, c1ok = lane + 32 < w;
+
+    // ---- sweep 0: signs and the largest magnitude (T1Encoder.cpp:139-171) ----
+    uint32_t mx = 0;
+    for (int y = 0; y < h; ++y) {
+        const uint32_t m0 = c0ok ? load_smag(blk, lane, y) : 0u, m1 = c1ok ? load_smag(blk, lane + 32, y) : 0u;
+        mx = max(mx, max(m0 & 0x7fffffffu, m1 & 0x7fffffffu));
+        const uint32_t lo = __ballot_sync(FULL, m0 >> 31), hi = __ballot_sync(FULL, m1 >> 31);
+        if (lane == 0) R.sgn[y + 1] = (u64)lo | ((u64)hi << 32);
+    }
+    mx = __reduce_max_sync(FULL, mx);
+    int numbps = mx ? (32 - __clz(mx)) - 6 : 0;               // t1_opt.cpp:680
+    if (numbps < 0) numbps = 0;
+    const int npasses = numbps > 0 ? 3 * numbps - 2 : 0;
+    if (lane == 0) { res.numbps = numbps; res.npasses = npasses; res.status = 0; res.total = 0; res.nsym = 0; }
+    if (numbps == 0) return;
+    __syncwarp();
+
+    uint8_t* sym = sym_arena + (size_t)blk.sym_off * 16;
+    uint32_t* pn = pass_nsym + (size_t)bi * T1_MAX_PASSES;
+    const int nstripes = (h + 3) >> 2;
+    const u64 colmask = w == 64 ? ~0ull : ((1ull << w) - 1);
+    uint32_t done = 0;
+    int passno = 0;
+    bool overflow = false;
+
+    for (int bp = numbps - 1; bp >= 0 && !overflow; --bp) {
+        const int one = bp + 6;
+        const bool first = bp == numbps - 1;
+        // ---- sweep A: this plane's bits; distortion of refinement and of all newly significant ----
+        int d_ref = 0, d_sig = 0;
+        for (int y = 0; y < h; ++y) {
+            const uint32_t m0 = c0ok ? (load_smag(blk, lane, y) & 0x7fffffffu) : 0u;
+            const uint32_t m1 = c1ok ? (load_smag(blk, lane + 32, y) & 0x7fffffffu) : 0u;
+            const uint32_t b0 = (m0 >> one) & 1u, b1 = (m1 >> one) & 1u;
+            const uint32_t lo = __ballot_sync(FULL, b0), hi = __ballot_sync(FULL, b1);
+            if (lane == 0) R.bit[y + 1] = (u64)lo | ((u64)hi << 32);
+            const u64 s0 = R.sig[y + 1];
+            if ((s0 >> lane) & 1ull) d_ref += nmsedec_ref(L, m0, bp); else if (b0) d_sig += nmsedec_sig(L, m0, bp);
+            if ((s0 >> (lane + 32)) & 1ull) d_ref += nmsedec_ref(L, m1, bp); else if (b1) d_sig += nmsedec_sig(L, m1, bp);
+        }
+        d_ref = __reduce_add_sync(FULL, d_ref);
+        d_sig = __reduce_add_sync(FULL, d_sig);
+        __syncwarp();
+        int d_sp = 0;
+        if (!first) {
+            // ---- significance propagation membership: fix-point over the row masks ----
+            u64 e[4], st[4], b[4], M[4], N[4];
+            const bool act = lane < nstripes;
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int i = act ? 4 * lane + r + 1 : 0;
+                const u64 s0 = R.sig[i], up = R.sig[i > 0 ? i - 1 : 0], dn = R.sig[i + 1];
+                const u64 valid = (act && i <= h) ? colmask : 0ull;
+                e[r] = ~s0 & valid;
+                b[r] = R.bit[i];
+                st[r] = (up << 1) | up | (up >> 1) | (s0 << 1) | (s0 >> 1) | (dn << 1) | dn | (dn >> 1);
+                M[r] = e[r] & st[r];
+                N[r] = M[r] & b[r];
+            }
+            bool changed;
+            do {
+                u64 upN = __shfl_up_sync(FULL, N[3], 1);
+                if (lane == 0) upN = 0;
+                changed = false;
+                u64 c, m;
+                c = (upN << 1) | upN | (upN >> 1) | (N[0] << 1) | (N[1] << 1);
+                m = e[0] & (st[0] | c); changed |= m != M[0]; M[0] = m; N[0] = m & b[0];
+                c = (N[0] << 1) | N[0] | (N[1] << 1) | (N[2] << 1);
+                m = e[1] & (st[1] | c); changed |= m != M[1]; M[1] = m; N[1] = m & b[1];
+                c = (N[1] << 1) | N[1] | (N[2] << 1) | (N[3] << 1);
+                m = e[2] & (st[2] | c); changed |= m != M[2]; M[2] = m; N[2] = m & b[2];
+                c = (N[2] << 1) | N[2] | (N[3] << 1);
+                m = e[3] & (st[3] | c); changed |= m != M[3]; M[3] = m; N[3] = m & b[3];
+            } while (__any_sync(FULL, changed));
+            if (act) {
+#pragma unroll
+                for (int r = 0; r < 4; ++r) { R.mem[4 * lane + r + 1] = M[r]; R.nsp[4 * lane + r + 1] = N[r]; }
+            }
+            __syncwarp();
+            // ---- pass: significance propagation ----
+            uint32_t n = emit_pass<PASS_SIG>(R, L, blk, lane, sym, done, blk.sym_cap, overflow);
+            if (overflow) break;
+            done += n;
+            // distortion of the samples that became significant in this pass
+            for (int y = 0; y < h; ++y) {
+                const u64 np = R.nsp[y + 1];
+                if (!np) continue;
+                if ((np >> lane) & 1ull) d_sp += nmsedec_sig(L, load_smag(blk, lane, y) & 0x7fffffffu, bp);
+                if ((np >> (lane + 32)) & 1ull) d_sp += nmsedec_sig(L, load_smag(blk, lane + 32, y) & 0x7fffffffu, bp);
+            }
+            d_sp = __reduce_add_sync(FULL, d_sp);
+            if (lane == 0) { pn[passno] = n; res.nmsedec[passno] = d_sp; }
+            ++passno;
+            // ---- pass: magnitude refinement ----
+            n = emit_pass<PASS_REF>(R, L, blk, lane, sym, done, blk.sym_cap, overflow);
+            if (overflow) break;
+            done += n;
+            if (lane == 0) { pn[passno] = n; res.nmsedec[passno] = d_ref; }
+            ++passno;
+        }
+        // ---- pass: cleanup ----
+        {
+            uint32_t n = emit_pass<PASS_CLN>(R, L, blk, lane, sym, done, blk.sym_cap, overflow);
+            if (overflow) break;
+            done += n;
+            if (lane == 0) { pn[passno] = n; res.nmsedec[passno] = d_sig - d_sp; }
+            ++passno;
+        }
+        __syncwarp();
+        // ---- state for the next plane ----
+        for (int i = lane + 1; i <= h; i += 32) {
+            const u64 s0 = R.sig[i], b1 = s0 | R.nsp[i];
+            const u64 ncl = ~(b1 | R.mem[i]) & colmask & R.bit[i];
+            if (!first) R.ref[i] = s0;
+            R.sig[i] = b1 | ncl;
+            R.mem[i] = 0; R.nsp[i] = 0;
+        }
+        __syncwarp();
+    }
+    if (lane == 0) { res.nsym = done; if (overflow) res.status = 1; }
+}
+
+// ---- MQ coder ----------------------------------------------------------------------------------
+constexpr int MQ_THREADS = 128;
+
+struct MqEnc {
+    uint32_t a, c, ct;
+    int nb;                   // index of the last byte produced (bp - start); -1 = none yet
+    uint32_t last;            // that byte, still in a register (a later carry may bump it)
+    uint8_t* out;
+    int cap;
+    bool overflow;
+    __device__ __forceinline__ void advance(uint32_t byte) {
+        if (nb >= 0) { if (nb < cap) out[nb] = (uint8_t)last; else overflow = true; }
+        ++nb;
+        last = byte & 0xffu;
+    }
+    __device__ void byteout() {                                // mqc.cpp:223-257
+        if (nb < 0) { advance(c >> 19); c &= 0x7ffffu; ct = 8; }
+        else if (last == 0xffu) { advance(c >> 20); c &= 0xfffffu; ct = 7; }
+        else if ((c & 0x8000000u) == 0) { advance(c >> 19); c &= 0x7ffffu; ct = 8; }
+        else {
+            ++last;
+            if (last == 0xffu) { c &= 0x7ffffffu; advance(c >> 20); c &= 0xfffffu; ct = 7; }
+            else { advance(c >> 19); c &= 0x7ffffu; ct = 8; }
+        }
+    }
+    __device__ __forceinline__ void renorm() {                 // mqc.cpp:259-269, shift count taken at once
+        uint32_t n = __clz(a) - 16;
+        while (n) {
+            const uint32_t k = n < ct ? n : ct;
+            a <<= k; c <<= k; ct -= k; n -= k;
+            if (ct == 0) byteout();
+        }
+    }
+};
+
+__global__ void __launch_bounds__(MQ_THREADS)
+k_t1_mq(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __restrict__ tab,
+        const uint8_t* __restrict__ sym_arena, const uint32_t* __restrict__ pass_nsym,
+        uint8_t* __restrict__ out_arena, T1Result* __restrict__ results, int lanes) {
+    __shared__ uint32_t s_mq[96];
+    __shared__ uint32_t s_ctx[T1_NCTX][MQ_THREADS];
+    if (threadIdx.x < 94) s_mq[threadIdx.x] = tab->mq[threadIdx.x];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int gwarp = blockIdx.x * (MQ_THREADS / 32) + (threadIdx.x >> 5);
+    const int bi = gwarp * lanes + lane;
+    if (lane >= lanes || bi >= nblocks) return;
+    T1Result& res = results[bi];
+    const int npasses = res.npasses;
+    if (npasses == 0 || res.status != 0) { res.total = 0; return; }
+    const T1Block blk = blocks[bi];
+    const int t = threadIdx.x;
+#pragma unroll
+    for (int k = 0; k < T1_NCTX; ++k) s_ctx[k][t] = 0;
+    s_ctx[CTX_UNI][t] = 46 * 2; s_ctx[CTX_AGG][t] = 3 * 2; s_ctx[CTX_ZC][t] = 4 * 2;     // t1_opt.cpp:686-690
+
+    MqEnc q;
+    q.a = 0x8000u; q.c = 0; q.ct = 12; q.nb = -1; q.last = 0;                           // mqc.cpp:406-420
+    q.out = out_arena + blk.out_off; q.cap = (int)blk.out_cap; q.overflow = false;
+    const uint32_t* sp = reinterpret_cast<const uint32_t*>(sym_arena + (size_t)blk.sym_off * 16);
+    const uint32_t* pn = pass_nsym + (size_t)bi * T1_MAX_PASSES;
+    uint32_t pos = 0, word = 0;
+    for (int pass = 0; pass < npasses; ++pass) {
+        const uint32_t n = pn[pass];
+        for (uint32_t i = 0; i < n; ++i, ++pos) {
+            if ((pos & 3u) == 0) word = __ldg(sp + (pos >> 2));
+            const uint32_t s = (word >> ((pos & 3u) * 8)) & 0xffu;
+            const uint32_t ctx = s >> 1, d = s & 1u;
+            const uint32_t st = s_ctx[ctx][t];
+            const uint32_t e = s_mq[st];
+            const uint32_t qe = e & 0xffffu;
+            q.a -= qe;
+            if (d == (st & 1u)) {                              // MPS, mqc.cpp:271-285
+                if (q.a & 0x8000u) { q.c += qe; }
+                else {
+                    if (q.a < qe) q.a = qe; else q.c += qe;
+                    s_ctx[ctx][t] = (e >> 16) & 0xffu;
+                    q.renorm();
+                }
+            } else {                                           // LPS, mqc.cpp:287-297
+                if (q.a < qe) q.c += qe; else q.a = qe;
+                s_ctx[ctx][t] = e >> 24;
+                q.renorm();
+            }
+        }
+        res.rate[pass] = (q.nb < 0 ? 0 : q.nb) + 3;            // t1_opt.cpp:719
+    }
+    // flush, mqc.cpp:299-306, 441-452
+    {
+        const uint32_t tempc = q.c + q.a;
+        q.c |= 0xffffu;
+        if (q.c >= tempc) q.c -= 0x8000u;
+        q.c <<= q.ct; q.byteout();
+        q.c <<= q.ct; q.byteout();
+    }
+    if (q.nb >= 0) { if (q.nb < q.cap) q.out[q.nb] = (uint8_t)q.last; else q.overflow = true; }
+    int total = q.nb < 0 ? 0 : q.nb;
+    if (q.last != 0xffu) ++total;
+    if (q.overflow) { res.status = 2; res.total = 0; return; }
+    int lastrate = 0;
+    for (int pass = 0; pass < npasses; ++pass) {               // t1_opt.cpp:727-736
+        int r = res.rate[pass];
+        if (r > total) r = total;
+        if (r > 1 && q.out[r - 1] == 0xffu) --r;
+        res.rate[pass] = r;
+        lastrate = r;
+    }
+    res.total = lastrate;
+}
+
+// ---- compaction: exclusive scan of the kept byte counts, then one warp copies one block --------
+__global__ void __launch_bounds__(1024) k_t1_scan(const T1Result* __restrict__ results, int nblocks, uint32_t* __restrict__ offsets) {
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_carry;
+    if (threadIdx.x == 0) s_carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int base = 0; base < nblocks; base += 1024) {
+        const int i = base + threadIdx.x;
+        const uint32_t v = i < nblocks ? (uint32_t)results[i].total : 0u;
+        uint32_t incl = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += t; }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t w = s_warp[lane], wi = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(FULL, wi, d); if (lane >= d) wi += t; }
+            s_warp[lane] = wi - w;
+        }
+        __syncthreads();
+        const uint32_t excl = s_carry + s_warp[warp] + incl - v;
+        if (i < nblocks) offsets[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) s_carry = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) offsets[nblocks] = s_carry;
+}
+
+__global__ void __launch_bounds__(256) k_t1_gather(const T1Block* __restrict__ blocks, int nblocks, const uint8_t* __restrict__ out_arena,
+                                                  const T1Result* __restrict__ results, const uint32_t* __restrict__ offsets,
+                                                  uint8_t* __restrict__ packed) {
+    const int bi = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (bi >= nblocks) return;
+    const int n = results[bi].total;
+    const uint8_t* src = out_arena + blocks[bi].out_off;
+    uint8_t* dst = packed + offsets[bi];
+    for (int i = lane; i < n; i += 32) dst[i] = src[i];
+}
+
+}  // namespace
+
+void launch_t1_context(const T1Block* d_blocks, int nblocks, uint8_t* sym_arena, uint32_t* pass_nsym,
+                       T1Result* results, cudaStream_t st) {
+    if (nblocks <= 0) return;
+    k_t1_context<<<(nblocks + CX_WARPS - 1) / CX_WARPS, 32 * CX_WARPS, 0, st>>>(d_blocks, nblocks, t1_tables_device(), sym_arena, pass_nsym, results);
+}
+
+void launch_t1_mq(const T1Block* d_blocks, int nblocks, const uint8_t* sym_arena, const uint32_t* pass_nsym,
+                  uint8_t* out_arena, T1Result* results, int lanes_per_warp, cudaStream_t st) {
+    if (nblocks <= 0) return;
+    if (lanes_per_warp < 1) lanes_per_warp = 1;
+    if (lanes_per_warp > 32) lanes_per_warp = 32;
+    const int warps = (nblocks + lanes_per_warp - 1) / lanes_per_warp;
+    const int wpc = MQ_THREADS / 32;
+    k_t1_mq<<<(warps + wpc - 1) / wpc, MQ_THREADS, 0, st>>>(d_blocks, nblocks, t1_tables_device(), sym_arena, pass_nsym, out_arena, results, lanes_per_warp);
+}
+
+void launch_t1_compact(const T1Block* d_blocks, int nblocks, const uint8_t* out_arena, const T1Result* results,
+                       uint32_t* d_offsets, uint8_t* packed, cudaStream_t st) {
+    if (nblocks <= 0) return;
+    k_t1_scan<<<1, 1024, 0, st>>>(results, nblocks, d_offsets);
+    k_t1_gather<<<(nblocks + 7) / 8, 256, 0, st>>>(d_blocks, nblocks, out_arena, results, d_offsets, packed);
+}
+
+}  // namespace j2k
