@@ -1,0 +1,467 @@
+// Persistent encoder context: device buffers, block tables and the launch sequence
+//   upload -> MCT -> DWT levels -> Tier-1 context -> Tier-1 MQ -> compaction -> D2H -> host Tier-2.
+// Mirrors the order of opj_tcd_encode_tile (ext/grok/src/lib/openjp2/tcd.cpp:1000-1104); the hand-off
+// of per-block results to the host Tier-2 is the one the reference defines for accelerators
+// (plugin_bridge.cpp:72-174).  There is no CPU fallback for the pixel path.
+#include "../../include/j2kcuda.h"
+#include "common.h"
+#include "device.h"
+#include "t2.h"
+#include <algorithm>
+#include <chrono>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+using namespace j2k;
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) return set_error(J2KCUDA_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+struct j2kcuda_encoder {
+    j2kcuda_params p;
+    CodingParams cp;
+    int device = 0;
+    cudaStream_t st = nullptr;
+    int W = 0, H = 0, ncomp = 0, pitch = 0, numres = 0, irreversible = 0;
+    int32_t* planeA[4] = {nullptr, nullptr, nullptr, nullptr};
+    int32_t* planeB[4] = {nullptr, nullptr, nullptr, nullptr};
+    // pixel staging
+    uint8_t* d_pix = nullptr; size_t d_pix_cap = 0;
+    uint8_t* h_pix = nullptr; size_t h_pix_cap = 0;
+    PixelSrc src;
+    MctParams mp;
+    bool have_input = false;
+    // geometry
+    std::vector<EncTile> tiles;
+    std::vector<std::vector<DwtJob>> level_jobs;     // [level-1]
+    std::vector<int> level_items, level_seg;
+    DwtJob* d_jobs = nullptr;                        // all levels, concatenated
+    std::vector<int> level_off;
+    // tier-1
+    int nblocks = 0;
+    std::vector<T1Block> h_blocks;
+    std::vector<int> blk_tile, blk_index;            // global block -> (tile, index in tile)
+    T1Block* d_blocks = nullptr;
+    uint8_t* d_sym = nullptr; size_t sym_bytes = 0;
+    uint8_t* d_out = nullptr; size_t out_bytes = 0;
+    uint32_t* d_pass_nsym = nullptr;
+    T1Result* d_results = nullptr;
+    uint32_t* d_offsets = nullptr;
+    uint8_t* d_packed = nullptr;
+    T1Result* h_results = nullptr;                   // pinned
+    uint32_t* h_offsets = nullptr;                   // pinned
+    uint8_t* h_packed = nullptr; size_t h_packed_cap = 0;   // pinned
+    std::vector<std::vector<double>> dist;           // per block cumulative distortion
+    int mq_lanes = 32;
+    // timing
+    cudaEvent_t ev[10];
+    float ms[8] = {0};
+    uint64_t counters[6] = {0};
+    bool ran = false;
+};
+
+static void free_encoder(j2kcuda_encoder* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    for (int c = 0; c < 4; ++c) { cudaFree(e->planeA[c]); cudaFree(e->planeB[c]); }
+    cudaFree(e->d_pix); cudaFreeHost(e->h_pix);
+    cudaFree(e->d_jobs); cudaFree(e->d_blocks); cudaFree(e->d_sym); cudaFree(e->d_out);
+    cudaFree(e->d_pass_nsym); cudaFree(e->d_results); cudaFree(e->d_offsets); cudaFree(e->d_packed);
+    cudaFreeHost(e->h_results); cudaFreeHost(e->h_offsets); cudaFreeHost(e->h_packed);
+    for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
+    if (e->st) cudaStreamDestroy(e->st);
+    delete e;
+}
+
+static int setup_encoder(j2kcuda_encoder* e) {
+    const j2kcuda_params& p = e->p;
+    if (!p.width || !p.height || p.ncomp < 1 || p.ncomp > 4 || p.prec < 1 || p.prec > 16)
+        return set_error(J2KCUDA_ERR_PARAM, "unsupported image geometry (1-4 components, 1-16 bits)");
+    setup_coding_params(p, e->cp);
+    const CodingParams& cp = e->cp;
+    e->W = (int)p.width; e->H = (int)p.height; e->ncomp = (int)p.ncomp;
+    e->pitch = (e->W + 3) & ~3;
+    e->numres = cp.comps[0].numres;
+    e->irreversible = cp.comps[0].qmfbid == 0;
+    for (int c = 0; c < e->ncomp; ++c) {
+        if (cp.comps[c].numres != e->numres || cp.comps[c].dx != 1 || cp.comps[c].dy != 1)
+            return set_error(J2KCUDA_ERR_UNSUPPORTED, "sub-sampled components are not supported by the encoder");
+        if ((1 << cp.comps[c].cblkw) > 64 || (1 << cp.comps[c].cblkh) > 64)
+            return set_error(J2KCUDA_ERR_UNSUPPORTED, "code-blocks larger than 64x64 samples");
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return set_error(J2KCUDA_ERR_NO_DEVICE, "no CUDA device: libj2kcuda has no CPU path");
+    if (p.device >= 0) e->device = p.device; else cudaGetDevice(&e->device);
+    CK(cudaSetDevice(e->device));
+    if (const char* err = device_tables_init()) return set_error(J2KCUDA_ERR_CUDA, err);
+    CK(cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking));
+    for (auto& ev : e->ev) CK(cudaEventCreate(&ev));
+    const size_t plane_bytes = (size_t)e->pitch * e->H * sizeof(int32_t);
+    for (int c = 0; c < e->ncomp; ++c) {
+        CK(cudaMalloc(&e->planeA[c], plane_bytes));
+        CK(cudaMalloc(&e->planeB[c], plane_bytes));
+    }
+    // ---- geometry: tiles, DWT jobs per level, block table ----
+    const int nt = (int)(cp.tw * cp.th);
+    e->tiles.resize(nt);
+    const int levels = e->numres - 1;
+    e->level_jobs.assign(levels, {});
+    size_t sym_units = 0, out_off = 0;
+    for (int t = 0; t < nt; ++t) {
+        init_enc_tile(cp, t, e->tiles[t]);
+        const TileGeo& g = e->tiles[t].geo;
+        for (int c = 0; c < e->ncomp; ++c) {
+            const CompGeo& cg = g.comps[c];
+            const size_t origin = (size_t)cg.r.y0 * e->pitch + cg.r.x0;
+            for (int l = 1; l <= levels; ++l) {
+                const ResGeo& in = cg.res[e->numres - l];          // region this level transforms
+                if (in.r.w() <= 0 || in.r.h() <= 0) continue;
+                DwtJob j;
+                int32_t* from = ((l - 1) & 1) ? e->planeB[c] : e->planeA[c];
+                int32_t* to = (l & 1) ? e->planeB[c] : e->planeA[c];
+                j.src = from + origin; j.dst = to + origin;
+                j.x0 = in.r.x0; j.y0 = in.r.y0; j.x1 = in.r.x1; j.y1 = in.r.y1;
+                j.pitch = e->pitch; j.strip0 = 0; j.nstrips = 0; j.nsegs = 0;
+                e->level_jobs[l - 1].push_back(j);
+            }
+            (void)origin;
+        }
+        for (size_t k = 0; k < g.cblks.size(); ++k) {
+            const CblkGeo& cb = g.cblks[k];
+            const CompGeo& cg = g.comps[cb.comp];
+            const BandGeo& band = cg.res[cb.res].bands[cb.band];
+            T1Block b;
+            memset(&b, 0, sizeof(b));
+            const int level = cb.res == 0 ? levels : e->numres - cb.res;     // decomposition level holding the band
+            const int32_t* plane = levels == 0 ? e->planeA[cb.comp] : ((level & 1) ? e->planeB[cb.comp] : e->planeA[cb.comp]);
+            b.coeff = plane + (size_t)(cg.r.y0 + cb.py) * e->pitch + (cg.r.x0 + cb.px);
+            b.pitch = e->pitch;
+            b.w = (uint16_t)cb.r.w(); b.h = (uint16_t)cb.r.h();
+            b.orient = (uint8_t)cb.orient;
+            b.qmfbid = (uint8_t)cp.comps[cb.comp].qmfbid;
+            b.max_planes = (uint16_t)std::max(band.numbps, 1);
+            b.bandconst = band_const(band.stepsize);
+            // worst case per plane: one decision per sample plus two extra per run-length column,
+            // and one sign per sample overall
+            const size_t area = (size_t)b.w * b.h;
+            size_t cap = area * ((size_t)b.max_planes + 2) * 3 / 2 + area + 64;
+            cap = (cap + 15) & ~(size_t)15;
+            b.sym_off = (uint32_t)sym_units; b.sym_cap = (uint32_t)cap;
+            sym_units += cap / 16;
+            size_t ocap = 64 + area * ((size_t)b.max_planes + 2) / 4;
+            ocap = (ocap + 15) & ~(size_t)15;
+            b.out_off = (uint32_t)out_off; b.out_cap = (uint32_t)ocap;
+            out_off += ocap;
+            e->h_blocks.push_back(b);
+            e->blk_tile.push_back(t); e->blk_index.push_back((int)k);
+        }
+    }
+    if (sym_units * 16 > 0xffffffffull * 16 || out_off > 0xffffffffull)
+        return set_error(J2KCUDA_ERR_UNSUPPORTED, "frame too large for 32-bit arena offsets");
+    e->nblocks = (int)e->h_blocks.size();
+    e->sym_bytes = sym_units * 16; e->out_bytes = out_off;
+    // DWT job tables
+    std::vector<DwtJob> all;
+    e->level_off.assign(levels, 0); e->level_items.assign(levels, 0); e->level_seg.assign(levels, 0);
+    for (int l = 0; l < levels; ++l) {
+        auto& v = e->level_jobs[l];
+        e->level_off[l] = (int)all.size();
+        if (v.empty()) continue;
+        e->level_items[l] = dwt_plan_jobs(v.data(), (int)v.size());
+        e->level_seg[l] = v[0].strip0;
+        all.insert(all.end(), v.begin(), v.end());
+    }
+    if (!all.empty()) {
+        CK(cudaMalloc(&e->d_jobs, all.size() * sizeof(DwtJob)));
+        CK(cudaMemcpy(e->d_jobs, all.data(), all.size() * sizeof(DwtJob), cudaMemcpyHostToDevice));
+    }
+    if (e->nblocks) {
+        CK(cudaMalloc(&e->d_blocks, e->nblocks * sizeof(T1Block)));
+        CK(cudaMemcpy(e->d_blocks, e->h_blocks.data(), e->nblocks * sizeof(T1Block), cudaMemcpyHostToDevice));
+        CK(cudaMalloc(&e->d_sym, e->sym_bytes));
+        CK(cudaMalloc(&e->d_out, e->out_bytes));
+        CK(cudaMalloc(&e->d_packed, e->out_bytes));
+        CK(cudaMalloc(&e->d_pass_nsym, (size_t)e->nblocks * T1_MAX_PASSES * sizeof(uint32_t)));
+        CK(cudaMalloc(&e->d_results, (size_t)e->nblocks * sizeof(T1Result)));
+        CK(cudaMalloc(&e->d_offsets, ((size_t)e->nblocks + 1) * sizeof(uint32_t)));
+        CK(cudaMallocHost(&e->h_results, (size_t)e->nblocks * sizeof(T1Result)));
+        CK(cudaMallocHost(&e->h_offsets, ((size_t)e->nblocks + 1) * sizeof(uint32_t)));
+    }
+    e->dist.assign(e->nblocks, {});
+    if (const char* s = getenv("J2KCUDA_MQ_LANES")) { int v = atoi(s); if (v >= 1 && v <= 32) e->mq_lanes = v; }
+    // sample conversion parameters
+    memset(&e->mp, 0, sizeof(e->mp));
+    e->mp.width = e->W; e->mp.height = e->H; e->mp.pitch = e->pitch; e->mp.ncomp = e->ncomp;
+    e->mp.mct = cp.mct ? 1 : 0; e->mp.irreversible = e->irreversible;
+    for (int c = 0; c < e->ncomp; ++c) {
+        e->mp.prec[c] = cp.comps[c].prec;
+        e->mp.dc_shift[c] = cp.comps[c].sgnd ? 0 : 1 << (cp.comps[c].prec - 1);
+    }
+    return J2KCUDA_OK;
+}
+
+static int sample_bytes_of(int sample_type) {
+    return sample_type == J2KCUDA_UCHAR ? 1 : (sample_type == J2KCUDA_USHORT ? 2 : 4);
+}
+
+// Host planes -> device.  One DMA per contiguous host range: directly from the caller's memory when
+// it is page-locked, through the context's pinned staging buffer otherwise.
+static int upload_planes(j2kcuda_encoder* e, const j2kcuda_plane* planes, int nplanes) {
+    if (nplanes < e->ncomp) return set_error(J2KCUDA_ERR_PARAM, "fewer planes than components");
+    const int S = sample_bytes_of(planes[0].sample_type);
+    struct Range { const uint8_t* lo; const uint8_t* hi; size_t dev; };
+    std::vector<Range> ranges;
+    for (int c = 0; c < e->ncomp; ++c) {
+        const j2kcuda_plane& pl = planes[c];
+        if (!pl.buf || (int)pl.width != e->W || (int)pl.height != e->H)
+            return set_error(J2KCUDA_ERR_PARAM, "plane size differs from the image size");
+        if (sample_bytes_of(pl.sample_type) != S || pl.colbytes < S || pl.rowbytes < 0)
+            return set_error(J2KCUDA_ERR_PARAM, "planes must share one sample type and have positive strides");
+        const uint8_t* lo = (const uint8_t*)pl.buf;
+        const uint8_t* hi = lo + (size_t)(e->H - 1) * pl.rowbytes + (size_t)(e->W - 1) * pl.colbytes + S;
+        ranges.push_back({lo, hi, 0});
+    }
+    // merge overlapping / adjacent ranges
+    std::vector<Range> merged;
+    {
+        std::vector<Range> s = ranges;
+        std::sort(s.begin(), s.end(), [](const Range& a, const Range& b) { return a.lo < b.lo; });
+        for (auto& r : s) {
+            if (!merged.empty() && r.lo <= merged.back().hi) { if (r.hi > merged.back().hi) merged.back().hi = r.hi; }
+            else merged.push_back(r);
+        }
+    }
+    size_t total = 0;
+    for (auto& m : merged) {
+        total = (total + 255) & ~(size_t)255;
+        total += (uintptr_t)m.lo & 15;                 // keep the caller's alignment modulo 16
+        m.dev = total;
+        total += (size_t)(m.hi - m.lo);
+    }
+    if (total > e->d_pix_cap) {
+        cudaFree(e->d_pix); e->d_pix = nullptr; e->d_pix_cap = 0;
+        CK(cudaMalloc(&e->d_pix, total + 256));
+        e->d_pix_cap = total;
+    }
+    uint64_t h2d = 0;
+    for (auto& m : merged) {
+        const size_t n = (size_t)(m.hi - m.lo);
+        cudaPointerAttributes attr;
+        bool pinned = cudaPointerGetAttributes(&attr, m.lo) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+        cudaGetLastError();
+        if (pinned) {
+            CK(cudaMemcpyAsync(e->d_pix + m.dev, m.lo, n, cudaMemcpyHostToDevice, e->st));
+        } else {
+            if (total > e->h_pix_cap) {
+                CK(cudaStreamSynchronize(e->st));
+                cudaFreeHost(e->h_pix); e->h_pix = nullptr; e->h_pix_cap = 0;
+                CK(cudaMallocHost(&e->h_pix, total + 256));
+                e->h_pix_cap = total;
+            }
+            const size_t chunk = 4u << 20;
+            for (size_t off = 0; off < n; off += chunk) {
+                const size_t k = std::min(chunk, n - off);
+                memcpy(e->h_pix + m.dev + off, m.lo + off, k);
+                CK(cudaMemcpyAsync(e->d_pix + m.dev + off, e->h_pix + m.dev + off, k, cudaMemcpyHostToDevice, e->st));
+            }
+        }
+        h2d += n;
+    }
+    memset(&e->src, 0, sizeof(e->src));
+    e->src.sample_bytes = S;
+    e->src.sgnd = planes[0].sgnd;
+    for (int c = 0; c < e->ncomp; ++c) {
+        const uint8_t* lo = (const uint8_t*)planes[c].buf;
+        for (auto& m : merged)
+            if (lo >= m.lo && lo < m.hi) { e->src.base[c] = e->d_pix + m.dev + (lo - m.lo); break; }
+        e->src.colbytes[c] = planes[c].colbytes;
+        e->src.rowbytes[c] = planes[c].rowbytes;
+        const int depth = planes[c].depth ? planes[c].depth : e->mp.prec[c];
+        e->mp.in_depth[c] = depth;
+        e->mp.in_shift[c] = e->mp.prec[c] - depth;
+    }
+    e->counters[4] = h2d;
+    e->have_input = true;
+    return J2KCUDA_OK;
+}
+
+extern "C" {
+
+j2kcuda_encoder* j2kcuda_encoder_create(const j2kcuda_params* p) {
+    if (!p) { set_error(J2KCUDA_ERR_PARAM, "null params"); return nullptr; }
+    j2kcuda_encoder* e = new j2kcuda_encoder();
+    for (auto& ev : e->ev) ev = nullptr;
+    e->p = *p;
+    if (setup_encoder(e) != J2KCUDA_OK) { free_encoder(e); return nullptr; }
+    return e;
+}
+
+void j2kcuda_encoder_destroy(j2kcuda_encoder* e) { free_encoder(e); }
+
+int j2kcuda_encoder_upload(j2kcuda_encoder* e, const j2kcuda_plane* planes, int nplanes) {
+    if (!e || !planes) return set_error(J2KCUDA_ERR_PARAM, "null argument");
+    CK(cudaSetDevice(e->device));
+    CK(cudaEventRecord(e->ev[8], e->st));
+    int rc = upload_planes(e, planes, nplanes);
+    if (rc) return rc;
+    CK(cudaEventRecord(e->ev[9], e->st));
+    return J2KCUDA_OK;
+}
+
+int j2kcuda_encoder_set_device_input(j2kcuda_encoder* e, const void* d_pixels, int64_t pitch_bytes, int sample_type) {
+    if (!e || !d_pixels) return set_error(J2KCUDA_ERR_PARAM, "null argument");
+    const int S = sample_bytes_of(sample_type);
+    memset(&e->src, 0, sizeof(e->src));
+    e->src.sample_bytes = S;
+    e->src.sgnd = (int)e->p.sgnd;
+    for (int c = 0; c < e->ncomp; ++c) {
+        e->src.base[c] = (const uint8_t*)d_pixels + (size_t)c * S;
+        e->src.colbytes[c] = (int64_t)e->ncomp * S;
+        e->src.rowbytes[c] = pitch_bytes;
+        e->mp.in_depth[c] = e->mp.prec[c];
+        e->mp.in_shift[c] = 0;
+    }
+    CK(cudaSetDevice(e->device));
+    CK(cudaEventRecord(e->ev[8], e->st));
+    CK(cudaEventRecord(e->ev[9], e->st));
+    e->counters[4] = 0;
+    e->have_input = true;
+    return J2KCUDA_OK;
+}
+
+int j2kcuda_encoder_run(j2kcuda_encoder* e) {
+    if (!e) return set_error(J2KCUDA_ERR_PARAM, "null encoder");
+    if (!e->have_input) return set_error(J2KCUDA_ERR_PARAM, "no input uploaded");
+    CK(cudaSetDevice(e->device));
+    cudaStream_t st = e->st;
+    uint64_t launches = 0;
+    CK(cudaEventRecord(e->ev[0], st));
+    launch_mct_forward(e->src, e->mp, e->planeA, st); ++launches;
+    CK(cudaEventRecord(e->ev[1], st));
+    const int levels = e->numres - 1;
+    for (int l = 0; l < levels; ++l) {
+        if (e->level_jobs[l].empty()) continue;
+        if (l == 1) CK(cudaEventRecord(e->ev[6], st));
+        launch_dwt_forward(e->d_jobs + e->level_off[l], (int)e->level_jobs[l].size(), e->level_items[l], e->level_seg[l],
+                           e->irreversible ? DWT_97_FIX : DWT_53, st);
+        ++launches;
+    }
+    if (levels < 2) CK(cudaEventRecord(e->ev[6], st));
+    CK(cudaEventRecord(e->ev[2], st));
+    launch_t1_context(e->d_blocks, e->nblocks, e->d_sym, e->d_pass_nsym, e->d_results, st); ++launches;
+    CK(cudaEventRecord(e->ev[3], st));
+    launch_t1_mq(e->d_blocks, e->nblocks, e->d_sym, e->d_pass_nsym, e->d_out, e->d_results, e->mq_lanes, st); ++launches;
+    CK(cudaEventRecord(e->ev[4], st));
+    launch_t1_compact(e->d_blocks, e->nblocks, e->d_out, e->d_results, e->d_offsets, e->d_packed, st); launches += 2;
+    if (e->nblocks) {
+        CK(cudaMemcpyAsync(e->h_results, e->d_results, (size_t)e->nblocks * sizeof(T1Result), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(e->h_offsets, e->d_offsets, ((size_t)e->nblocks + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    size_t packed = e->nblocks ? e->h_offsets[e->nblocks] : 0;
+    if (packed > e->h_packed_cap) {
+        cudaFreeHost(e->h_packed); e->h_packed = nullptr; e->h_packed_cap = 0;
+        size_t cap = packed + packed / 4 + 4096;
+        CK(cudaMallocHost(&e->h_packed, cap));
+        e->h_packed_cap = cap;
+    }
+    if (packed) CK(cudaMemcpyAsync(e->h_packed, e->d_packed, packed, cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(e->ev[5], st));
+    CK(cudaStreamSynchronize(st));
+    uint64_t nsym = 0;
+    for (int i = 0; i < e->nblocks; ++i) {
+        if (e->h_results[i].status != 0)
+            return set_error(J2KCUDA_ERR_CUDA, e->h_results[i].status == 1 ? "tier-1 symbol slot overflow" : "tier-1 byte slot overflow");
+        nsym += e->h_results[i].nsym;
+    }
+    cudaEventElapsedTime(&e->ms[0], e->ev[8], e->ev[9]);
+    cudaEventElapsedTime(&e->ms[1], e->ev[0], e->ev[1]);
+    cudaEventElapsedTime(&e->ms[2], e->ev[1], e->ev[2]);
+    cudaEventElapsedTime(&e->ms[3], e->ev[2], e->ev[3]);
+    cudaEventElapsedTime(&e->ms[4], e->ev[3], e->ev[4]);
+    cudaEventElapsedTime(&e->ms[5], e->ev[4], e->ev[5]);
+    cudaEventElapsedTime(&e->ms[7], e->ev[1], e->ev[6]);
+    e->counters[0] = launches; e->counters[1] = (uint64_t)e->nblocks; e->counters[2] = nsym;
+    e->counters[3] = packed;
+    e->counters[5] = (uint64_t)e->nblocks * sizeof(T1Result) + ((uint64_t)e->nblocks + 1) * 4 + packed;
+    e->ran = true;
+    return J2KCUDA_OK;
+}
+
+int j2kcuda_encoder_finish(j2kcuda_encoder* e, uint8_t** out, size_t* out_len) {
+    if (!e || !out || !out_len) return set_error(J2KCUDA_ERR_PARAM, "null argument");
+    if (!e->ran) return set_error(J2KCUDA_ERR_PARAM, "encoder_run has not completed");
+    auto t0 = std::chrono::steady_clock::now();
+    const CodingParams& cp = e->cp;
+    for (auto& t : e->tiles) init_enc_tile(cp, t.geo.tileno, t);
+    for (int i = 0; i < e->nblocks; ++i) {
+        const T1Result& r = e->h_results[i];
+        EncTile& tile = e->tiles[e->blk_tile[i]];
+        const CblkGeo& cb = tile.geo.cblks[e->blk_index[i]];
+        const BandGeo& band = tile.geo.comps[cb.comp].res[cb.res].bands[cb.band];
+        EncBlock& b = tile.blocks[e->blk_index[i]];
+        // cumulative weighted distortion, t1_opt.cpp:711-722 with t1.cpp:1114-1143
+        const bool real = cp.comps[cb.comp].qmfbid == 0;
+        const int level = cp.comps[cb.comp].numres - 1 - cb.res;
+        const double w1 = (cp.mct && cb.comp < 3 && cp.ncomp >= 3) ? mct_norm(cb.comp, real) : 1.0;
+        const double w2 = dwt_norm(level, cb.orient, real);
+        std::vector<double>& d = e->dist[i];
+        d.resize(r.npasses + 1);
+        double cum = 0;
+        int bpno = r.numbps - 1, passtype = 2;
+        for (int k = 0; k < r.npasses; ++k) {
+            double w = w1 * w2 * (double)band.stepsize * (double)(1 << bpno);
+            w *= w * r.nmsedec[k] / 8192.0;
+            cum += w;
+            d[k] = cum;
+            if (++passtype == 3) { passtype = 0; --bpno; }
+        }
+        b.data = e->h_packed + e->h_offsets[i];
+        b.numbps = r.numbps; b.totalpasses = r.npasses;
+        b.rates = r.rate; b.dist = d.data();
+    }
+    EncoderHost host;
+    host.cp = cp;
+    host.ntiles = (int)e->tiles.size();
+    std::vector<uint8_t> cs;
+    std::string err;
+    if (!host.assemble(e->tiles, cs, err)) return set_error(J2KCUDA_ERR_PARAM, err);
+    *out = (uint8_t*)malloc(cs.size() ? cs.size() : 1);
+    if (!*out) return set_error(J2KCUDA_ERR_NOMEM, "malloc");
+    memcpy(*out, cs.data(), cs.size());
+    *out_len = cs.size();
+    e->ms[6] = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return J2KCUDA_OK;
+}
+
+int j2kcuda_encoder_timings(j2kcuda_encoder* e, float* ms, int n) {
+    if (!e || !ms) return 0;
+    int k = n < 8 ? n : 8;
+    for (int i = 0; i < k; ++i) ms[i] = e->ms[i];
+    return k;
+}
+
+int j2kcuda_encoder_counters(j2kcuda_encoder* e, uint64_t* v, int n) {
+    if (!e || !v) return 0;
+    int k = n < 6 ? n : 6;
+    for (int i = 0; i < k; ++i) v[i] = e->counters[i];
+    return k;
+}
+
+int j2kcuda_encode(const j2kcuda_params* p, const j2kcuda_plane* planes, int nplanes, uint8_t** out, size_t* out_len) {
+    j2kcuda_encoder* e = j2kcuda_encoder_create(p);
+    if (!e) return J2KCUDA_ERR_PARAM;
+    int rc = j2kcuda_encoder_upload(e, planes, nplanes);
+    if (!rc) rc = j2kcuda_encoder_run(e);
+    if (!rc) rc = j2kcuda_encoder_finish(e, out, out_len);
+    j2kcuda_encoder_destroy(e);
+    return rc;
+}
+
+}  // extern "C"
