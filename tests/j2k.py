@@ -73,3 +73,54 @@ def encode(img, prec, **kw):
     data = C.string_at(out, n.value)
     L.lib().j2kcuda_free(out)
     return data
+
+
+def probe(data):
+    info = L.Info()
+    rc = L.lib().j2kcuda_probe(data, C.c_size_t(len(data)), C.byref(info))
+    assert rc == 0, L.last_error()
+    return info
+
+
+def t2_parse(data):
+    """-> list of (numbps, npasses, bytes) per code-block in Tier-2 order"""
+    info = C.POINTER(C.c_int32)(); nb = C.c_int(0); seg = C.POINTER(C.c_uint8)(); n = C.c_size_t(0)
+    rc = L.lib().j2kcuda_t2_parse(data, C.c_size_t(len(data)), 0, C.byref(info), C.byref(nb), C.byref(seg), C.byref(n))
+    assert rc == 0, L.last_error()
+    raw = C.string_at(seg, n.value)
+    out = []
+    for i in range(nb.value):
+        numbps, npasses, ln, off = info[4 * i], info[4 * i + 1], info[4 * i + 2], info[4 * i + 3]
+        out.append((numbps, npasses, raw[off:off + ln]))
+    L.lib().j2kcuda_free(info); L.lib().j2kcuda_free(seg)
+    return out
+
+
+def stage_t1_decode(blocks):
+    """blocks: list of (w, h, orient, numbps, npasses, bytes) -> list of (h, w) int32 arrays (reference
+    decoder representation: one extra fractional bit)"""
+    data = b"".join(b[5] for b in blocks)
+    blk = np.array([[b[0], b[1], b[2], b[3], b[4], len(b[5])] for b in blocks], dtype=np.int32)
+    total = int(sum(b[0] * b[1] for b in blocks))
+    out = np.zeros(max(total, 1), np.int32)
+    buf = np.frombuffer(data + b"\0", dtype=np.uint8).copy()
+    rc = L.lib().j2kcuda_stage_t1_decode(_vp(buf), _vp(blk), len(blocks), _vp(out))
+    assert rc == 0, L.last_error()
+    res, pos = [], 0
+    for b in blocks:
+        res.append(out[pos:pos + b[0] * b[1]].reshape(b[1], b[0]).copy())
+        pos += b[0] * b[1]
+    return res
+
+
+def decode(data, reduce=0, dtype=None):
+    """codestream -> (h, w, ncomp) array through j2kcuda_decode (host destination, interleaved)"""
+    info = probe(data)
+    w = -(-info.width // (1 << reduce)); h = -(-info.height // (1 << reduce)); nc = info.ncomp
+    if dtype is None:
+        dtype = np.uint8 if max(info.prec[c] for c in range(nc)) <= 8 else np.uint16
+    img = np.zeros((h, w, nc), dtype=dtype)
+    pl = planes_of(img)
+    rc = L.lib().j2kcuda_decode(data, C.c_size_t(len(data)), reduce, pl, nc, None, None)
+    assert rc == 0, L.last_error()
+    return img
