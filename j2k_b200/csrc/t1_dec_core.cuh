@@ -1,0 +1,271 @@
+// Tier-1 decoder core, shared between the CUDA kernel (t1_dec.cu) and a host-compiled test harness
+// (tests/native/t1dec_host.cpp) that runs the very same block routine with one "lane".  See t1_dec.cu.
+#pragma once
+#include "device.h"
+#include "t1_tables.cuh"
+#ifdef __CUDACC__
+#define J2K_HD __host__ __device__
+#else
+#define J2K_HD
+#endif
+#if defined(__CUDA_ARCH__)
+#define J2K_FFSLL(v) __ffsll((long long)(v))
+#define J2K_SYNCWARP() __syncwarp()
+#define J2K_FMUL(a, b) __fmul_rn((a), (b))
+#else
+#define J2K_FFSLL(v) __builtin_ffsll((long long)(v))
+#define J2K_SYNCWARP() ((void)0)
+#define J2K_FMUL(a, b) ((a) * (b))
+#endif
+
+namespace j2k {
+namespace t1dec {
+
+typedef unsigned long long u64;
+
+struct DRows {                // index = row + 1
+    u64 sig[66], sgn[66], vis[66], ref[66], bit[66], last[66];
+};
+
+struct MqDec {
+    uint32_t a, c, ct;
+    const uint8_t* bp;        // data is followed by two 0xFF bytes, which reproduces the reference's
+                              // behaviour at and past the end of the segment (mqc.cpp:336-365)
+    J2K_HD inline void bytein() {
+        const uint32_t cur = bp[0], nxt = bp[1];
+        if (cur == 0xffu) {
+            if (nxt > 0x8fu) { c += 0xff00u; ct = 8; }
+            else { ++bp; c += nxt << 9; ct = 7; }
+        } else { ++bp; c += nxt << 8; ct = 8; }
+    }
+    J2K_HD void init(const uint8_t* p) {                  // mqc.cpp:560-575
+        bp = p;
+        c = (uint32_t)p[0] << 16;
+        bytein();
+        c <<= 7; ct -= 7; a = 0x8000u;
+    }
+    J2K_HD inline void renorm() {
+        do {
+            if (ct == 0) bytein();
+            a <<= 1; c <<= 1; --ct;
+        } while (a < 0x8000u);
+    }
+    // st: per-context state (index*2 + mps), tab: T1Tables::mq
+    J2K_HD inline uint32_t decode(uint8_t* st, const uint32_t* tab, uint32_t ctx) {   // mqc.cpp:577-595
+        const uint32_t s = st[ctx], e = tab[s], qe = e & 0xffffu;
+        uint32_t d = s & 1u;
+        a -= qe;
+        if ((c >> 16) < qe) {
+            if (a < qe) st[ctx] = (uint8_t)((e >> 16) & 0xffu);
+            else { d ^= 1u; st[ctx] = (uint8_t)(e >> 24); }
+            a = qe;
+            renorm();
+        } else {
+            c -= qe << 16;
+            if ((a & 0x8000u) == 0) {
+                if (a < qe) { d ^= 1u; st[ctx] = (uint8_t)(e >> 24); }
+                else st[ctx] = (uint8_t)((e >> 16) & 0xffu);
+                renorm();
+            }
+        }
+        return d;
+    }
+};
+
+J2K_HD inline uint32_t w3(u64 m, int x) {          // bits x-1, x, x+1 of a row
+    return (uint32_t)(x ? (m >> (x - 1)) : (m << 1)) & 7u;
+}
+
+struct Stripe {               // rows q = 0..5 <-> y = 4*stripe - 1 + q
+    u64 S[6], G[6];           // significance, sign
+    u64 V[4], F[4], B[4], L[4];   // visited, refined, this plane's bits, coded in this plane
+};
+
+// zero-coding neighbourhood index of sample (x, row q) from the live significance rows
+J2K_HD inline uint32_t nbhood(const Stripe& s, int q, int x) {
+    const uint32_t up = w3(s.S[q - 1], x), mid = w3(s.S[q], x), dn = w3(s.S[q + 1], x);
+    return up | ((mid & 1u) << 3) | ((mid >> 2) << 4) | (dn << 5);
+}
+
+J2K_HD inline void decode_sign(Stripe& s, MqDec& mq, uint8_t* st, const uint32_t* tab, const uint8_t* sc, int q, int x) {
+    const uint32_t ms = w3(s.S[q], x), mg = w3(s.G[q], x);
+    const uint32_t sn = (w3(s.S[q - 1], x) >> 1) & 1u, ss = (w3(s.S[q + 1], x) >> 1) & 1u;
+    const uint32_t gn = (w3(s.G[q - 1], x) >> 1) & 1u, gs = (w3(s.G[q + 1], x) >> 1) & 1u;
+    const uint32_t sw = ms & 1u, se = ms >> 2;
+    const uint32_t idx = sw | (se << 1) | (sn << 2) | (ss << 3) | ((sw & mg) << 4) | ((se & (mg >> 2)) << 5) | ((sn & gn) << 6) | ((ss & gs) << 7);
+    const uint32_t e = sc[idx];
+    const uint32_t neg = mq.decode(st, tab, CTX_SC + (e & 7u)) ^ (e >> 3);
+    s.S[q] |= 1ull << x;
+    s.G[q] |= (u64)neg << x;
+    s.B[q - 1] |= 1ull << x;
+    s.L[q - 1] |= 1ull << x;
+}
+
+
+// Decode one code-block.  Called by all `nlanes` lanes of a warp with identical arguments except `lane`;
+// the decision loop runs redundantly on warp-uniform data, the lane index only partitions the
+// column-parallel parts (fold, final pass).  R and st must be zero / reset on entry.
+J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, uint8_t* st, const uint8_t* zc_all, const uint8_t* sc,
+                                const uint32_t* mqtab, const uint8_t* seg_arena, int raw_output, int lane, int nlanes) {
+    const int w = blk.w, h = blk.h;
+    int32_t* out = blk.coeff;
+    const uint8_t* zc = zc_all + blk.orient * 256;
+    const int nstripes = (h + 3) >> 2;
+    const u64 colmask = w == 64 ? ~0ull : ((1ull << w) - 1);
+
+    MqDec mq;
+    mq.init(seg_arena + blk.data_off);
+
+    int bp = blk.numbps - 1;              // 0-based bit-plane being decoded
+    int passtype = 2;
+    int lastplane = bp;
+    bool firstfold = true;
+    for (int passno = 0; passno < blk.npasses && bp >= 0; ++passno) {
+        for (int sidx = 0; sidx < nstripes; ++sidx) {
+            Stripe s;
+            const int ib = 4 * sidx;       // smem index of row q = 0
+#pragma unroll
+            for (int q = 0; q < 6; ++q) { s.S[q] = R.sig[ib + q]; s.G[q] = R.sgn[ib + q]; }
+            u64 valid[4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                s.V[r] = R.vis[ib + 1 + r]; s.F[r] = R.ref[ib + 1 + r]; s.B[r] = R.bit[ib + 1 + r]; s.L[r] = R.last[ib + 1 + r];
+                valid[r] = (ib + r < h) ? colmask : 0ull;
+            }
+            if (passtype == 0) {
+                // significance propagation: columns that have (or acquire) a significant sample in
+                // their 3x6 window
+                u64 active = 0;
+#pragma unroll
+                for (int q = 0; q < 6; ++q) active |= (s.S[q] << 1) | s.S[q] | (s.S[q] >> 1);
+                active &= colmask;
+                u64 donec = 0;
+                while (u64 rem = active & ~donec) {
+                    const int x = J2K_FFSLL(rem) - 1;
+                    donec |= 1ull << x;
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        const int q = r + 1;
+                        if (!((valid[r] >> x) & 1ull) || ((s.S[q] >> x) & 1ull)) continue;
+                        const uint32_t nb = nbhood(s, q, x);
+                        if (!nb) continue;
+                        if (mq.decode(st, mqtab, zc[nb])) {
+                            decode_sign(s, mq, st, mqtab, sc, q, x);
+                            active |= (2ull << x) & colmask;           // the next column may now hold candidates
+                        }
+                        s.V[r] |= 1ull << x;
+                    }
+                }
+            } else if (passtype == 1) {
+                // magnitude refinement: significant and not coded in this plane's first pass
+                u64 cols = 0;
+#pragma unroll
+                for (int r = 0; r < 4; ++r) cols |= s.S[r + 1] & ~s.V[r] & valid[r];
+                while (cols) {
+                    const int x = J2K_FFSLL(cols) - 1;
+                    cols &= cols - 1;
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        const int q = r + 1;
+                        if (!((s.S[q] & ~s.V[r] & valid[r]) >> x & 1ull)) continue;
+                        const uint32_t ctx = ((s.F[r] >> x) & 1ull) ? CTX_MAG + 2 : (nbhood(s, q, x) ? CTX_MAG + 1 : CTX_MAG);
+                        const uint32_t bit = mq.decode(st, mqtab, ctx);
+                        s.B[r] |= (u64)bit << x;
+                        s.L[r] |= 1ull << x;
+                        s.F[r] |= 1ull << x;
+                    }
+                }
+            } else {
+                // cleanup: everything not yet significant and not visited
+                u64 cols = 0;
+#pragma unroll
+                for (int r = 0; r < 4; ++r) cols |= ~s.S[r + 1] & ~s.V[r] & valid[r];
+                const bool fullstripe = ib + 3 < h;
+                while (cols) {
+                    const int x = J2K_FFSLL(cols) - 1;
+                    cols &= cols - 1;
+                    int rstart = 0;
+                    bool partial = false;
+                    if (fullstripe) {
+                        u64 anyw = 0, memall = ~0ull;
+#pragma unroll
+                        for (int q = 0; q < 6; ++q) anyw |= s.S[q];
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) memall &= ~s.S[r + 1] & ~s.V[r];
+                        const bool agg = ((memall >> x) & 1ull) && w3(anyw, x) == 0;
+                        if (agg) {
+                            if (!mq.decode(st, mqtab, CTX_AGG)) continue;
+                            int runlen = (int)mq.decode(st, mqtab, CTX_UNI);
+                            runlen = (runlen << 1) | (int)mq.decode(st, mqtab, CTX_UNI);
+                            rstart = runlen;
+                            partial = true;
+                        }
+                    }
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        const int q = r + 1;
+                        if (r < rstart) continue;
+                        const bool forced = partial && r == rstart;
+                        if (!forced && !((~s.S[q] & ~s.V[r] & valid[r]) >> x & 1ull)) continue;
+                        uint32_t bit = 1;
+                        if (!forced) bit = mq.decode(st, mqtab, zc[nbhood(s, q, x)]);
+                        if (bit) decode_sign(s, mq, st, mqtab, sc, q, x);
+                    }
+                }
+#pragma unroll
+                for (int r = 0; r < 4; ++r) s.V[r] = 0;
+            }
+            // write the stripe back (rows of the neighbouring stripes are unchanged)
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const int i = ib + 1 + r;
+                R.sig[i] = s.S[r + 1]; R.sgn[i] = s.G[r + 1]; R.vis[i] = s.V[r]; R.ref[i] = s.F[r]; R.bit[i] = s.B[r]; R.last[i] = s.L[r];
+            }
+            J2K_SYNCWARP();
+        }
+        lastplane = bp;
+        if (++passtype == 3 || passno + 1 == blk.npasses) {
+            // fold this plane's decoded bits into the magnitudes kept in the coefficient plane
+            const bool plane_done = passtype == 3;
+            for (int y = 0; y < h; ++y) {
+                const u64 b = R.bit[y + 1];
+                if (!b && !firstfold) continue;
+                for (int x = lane; x < w; x += nlanes) {
+                    int32_t* p = out + (size_t)y * blk.pitch + x;
+                    int32_t v = firstfold ? 0 : *p;
+                    *p = v | (int32_t)(((b >> x) & 1ull) << bp);
+                }
+            }
+            firstfold = false;
+            J2K_SYNCWARP();
+            if (plane_done) {
+                passtype = 0;
+                if (passno + 1 < blk.npasses && bp > 0) {
+                    for (int i = lane + 1; i <= h; i += nlanes) { R.bit[i] = 0; R.last[i] = 0; }
+                }
+                --bp;
+                J2K_SYNCWARP();
+            }
+        }
+    }
+    // final pass: mid-point reconstruction, sign, dequantisation (T1Decoder.cpp:77-99)
+    for (int y = 0; y < h; ++y) {
+        const u64 sg = R.sig[y + 1], ng = R.sgn[y + 1], la = R.last[y + 1];
+        for (int x = lane; x < w; x += nlanes) {
+            int32_t* p = out + (size_t)y * blk.pitch + x;
+            int32_t v = 0;
+            if ((sg >> x) & 1ull) {
+                const int32_t m = firstfold ? 0 : *p;
+                const int qlast = ((la >> x) & 1ull) ? lastplane : lastplane + 1;
+                const int32_t t1 = (m << 1) | (1 << qlast);          // one extra fractional bit, t1.cpp:419-445
+                v = ((ng >> x) & 1ull) ? -t1 : t1;
+            }
+            if (raw_output) *p = v;
+            else if (blk.qmfbid) *p = v / 2;
+            else *reinterpret_cast<float*>(p) = J2K_FMUL((float)v, blk.stepsize);
+        }
+    }
+}
+
+}  // namespace t1dec
+}  // namespace j2k

@@ -1,0 +1,27 @@
+// TEST INFRASTRUCTURE: compiles the Tier-1 decoder core (j2k_b200/csrc/t1_dec_core.cuh) for the host and
+// runs the very block routine the CUDA kernel runs, with a single "lane".  Lets the CPU suite check
+// the decoder logic against the oracle without a GPU.  Never linked into libj2kcuda.
+#include "../../j2k_b200/csrc/t1_dec_core.cuh"
+#include <cstring>
+#include <vector>
+
+using namespace j2k;
+using namespace j2k::t1dec;
+
+extern "C" int t1dec_host_block(const uint8_t* data, int len, int w, int h, int orient, int numbps, int npasses,
+                                const uint8_t* zc, const uint8_t* sc, const uint32_t* mq, int32_t* out) {
+    std::vector<uint8_t> seg(data, data + len);
+    seg.push_back(0xff); seg.push_back(0xff);
+    T1DecBlock b;
+    memset(&b, 0, sizeof(b));
+    b.coeff = out; b.pitch = w; b.w = (uint16_t)w; b.h = (uint16_t)h; b.orient = (uint8_t)orient; b.qmfbid = 1;
+    b.numbps = (uint8_t)numbps; b.npasses = (uint8_t)npasses; b.data_off = 0; b.data_len = (uint32_t)len; b.stepsize = 1.f;
+    memset(out, 0, sizeof(int32_t) * (size_t)w * h);
+    if (!npasses || !numbps || !w || !h) return 0;
+    static DRows R;
+    memset(&R, 0, sizeof(R));
+    uint8_t st[32] = {0};
+    st[CTX_UNI] = 46 * 2; st[CTX_AGG] = 3 * 2; st[CTX_ZC] = 4 * 2;
+    decode_block(b, R, st, zc, sc, mq, seg.data(), 1, 0, 1);
+    return 0;
+}
