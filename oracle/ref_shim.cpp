@@ -170,9 +170,19 @@ int ref_decode(const uint8_t* data, size_t len, int reduce, int nthreads,
             else if (opj_decode(codec, stream, image) && opj_end_decompress(codec, stream)) {
                 rc = 0;
                 info[0] = image->comps[0].w; info[1] = image->comps[0].h;
-                for (int c = 0; c < (int)image->numcomps && c < max_planes; ++c)
-                    memcpy(planes[c], image->comps[c].data,
-                           sizeof(int32_t) * (size_t)image->comps[c].w * image->comps[c].h);
+                /* Reference quirk: a single-tile image decoded at reduced resolution is handed out as the
+                   tile buffer itself (j2k.cpp:7685-7695), whose rows keep the FULL-resolution pitch
+                   although comps[c].w is the reduced width; read it with the pitch it really has. */
+                opj_codestream_info_v2_t* ci = opj_get_cstr_info(codec);
+                bool single = ci && ci->tw * ci->th == 1;
+                if (ci) opj_destroy_cstr_info(&ci);
+                for (int c = 0; c < (int)image->numcomps && c < max_planes; ++c) {
+                    const opj_image_comp_t& ic = image->comps[c];
+                    size_t pitch = ic.w;
+                    if (single && reduce > 0) pitch = (image->x1 - image->x0 + ic.dx - 1) / ic.dx;
+                    for (uint32_t y = 0; y < ic.h; ++y)
+                        memcpy(planes[c] + (size_t)y * ic.w, ic.data + (size_t)y * pitch, sizeof(int32_t) * ic.w);
+                }
             }
         }
     }
