@@ -41,11 +41,45 @@ def run(h, w, nc, prec, kind, reps=5, **kw):
     lib.j2kcuda_encoder_destroy(e)
 
 
+def run_decode(h, w, nc, prec, kind, reps=5, **kw):
+    lib = L.lib()
+    img = make_frame(h, w, nc, prec, kind, 0)
+    cs = j2k.encode(img, prec, **kw)
+    lib.j2kcuda_decoder_create.restype = C.c_void_p
+    d = C.c_void_p(lib.j2kcuda_decoder_create(-1))
+    out = np.zeros_like(img)
+    pl = j2k.planes_of(out)
+    for r in range(reps):
+        t0 = time.perf_counter()
+        assert lib.j2kcuda_decoder_prepare(d, cs, C.c_size_t(len(cs)), 0) == 0, L.last_error()
+        t1 = time.perf_counter()
+        assert lib.j2kcuda_decoder_run(d) == 0, L.last_error()
+        t2 = time.perf_counter()
+        assert lib.j2kcuda_decoder_download(d, pl, nc) == 0, L.last_error()
+        t3 = time.perf_counter()
+    assert np.array_equal(out, img)
+    ms = (C.c_float * 8)()
+    lib.j2kcuda_decoder_timings(d, ms, 7)
+    names = ["host_parse", "h2d", "t1", "idwt", "imct", "d2h", "idwt_l1"]
+    print("DECODE %dx%dx%d %d-bit %s: %d bytes" % (w, h, nc, prec, kind, len(cs)))
+    print("  " + "  ".join("%s=%.3f" % (a, b) for a, b in zip(names, ms)))
+    print("  wall: prepare %.2f run %.2f download %.2f ms -> %.1f MPix/s" % ((t1 - t0) * 1e3, (t2 - t1) * 1e3, (t3 - t2) * 1e3, w * h / (t3 - t0) / 1e6))
+    lib.j2kcuda_decoder_destroy(d)
+
+
+
+
 if __name__ == "__main__":
-    for kind in ("smooth", "noise"):
-        run(2160, 4096, 4, 16, kind, mct=1)
-    run(1080, 2048, 3, 8, "smooth", mct=1)
-    for lanes in (1, 4, 8, 16):
-        os.environ["J2KCUDA_MQ_LANES"] = str(lanes)
-        print("MQ lanes", lanes)
-        run(2160, 4096, 4, 16, "smooth", reps=3, mct=1)
+    if "decode" in sys.argv:
+        for kind in ("smooth", "noise"):
+            run_decode(2160, 4096, 4, 16, kind, mct=1)
+        run_decode(1080, 2048, 3, 8, "smooth", mct=1)
+    else:
+        for kind in ("smooth", "noise"):
+            run(2160, 4096, 4, 16, kind, mct=1)
+        run(1080, 2048, 3, 8, "smooth", mct=1)
+        for lanes in (1, 4, 8, 16):
+            os.environ["J2KCUDA_MQ_LANES"] = str(lanes)
+            print("MQ lanes", lanes)
+            run(2160, 4096, 4, 16, "smooth", reps=3, mct=1)
+
