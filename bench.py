@@ -69,7 +69,11 @@ def reference_encode_fn():
     import refgrok
     if refgrok.available():
         ncores = os.cpu_count() or 1
-        return (lambda planes: refgrok.encode(planes, PREC, mct=1, numresolution=6, threads=ncores)), "reference", ncores
+        def roundtrip(planes):
+            cs = refgrok.encode(planes, PREC, mct=1, numresolution=6, threads=ncores)
+            refgrok.decode(cs, threads=ncores)
+            return cs
+        return roundtrip, "reference", ncores
     import hostpipe                       # oracle port: scalar, single thread
     from j2k_b200 import _lib as L
 
@@ -96,12 +100,12 @@ def run_reference(args, rank):
         enc(planes[i % 2])
     dt = time.perf_counter() - t0
     v = args.steps * w * h / dt / 1e6
-    sample = "%d frame(s) of %dx%d 16-bit RGBA per step, ext/grok CPU encoder, %d threads" % (1, w, h, cores)
+    sample = "%d frame(s) of %dx%d 16-bit RGBA per step, ext/grok CPU encoder + decoder, %d threads" % (1, w, h, cores)
     print(json.dumps({
-        "impl": "reference", "metric": "4K lossless encode MPix/s", "value": v, "unit": "MPix/s", "n_gpus": args.gpus,
+        "impl": "reference", "metric": "4K lossless encode+decode MPix/s", "value": v, "unit": "MPix/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic (%s)" % args.kind,
-        "config": {"workload": WORKLOAD, "direction": "encode"},
+        "config": {"workload": WORKLOAD, "direction": "encode then decode of the same frame"},
         "cpu_baseline": {"value": v, "unit": "MPix/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "MPix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
@@ -154,22 +158,42 @@ def main():
     ms = (C.c_float * 8)()
     cnt = (C.c_uint64 * 6)()
 
+    lib.j2kcuda_decoder_create.restype = C.c_void_p
+    dec = C.c_void_p(lib.j2kcuda_decoder_create(local))
+    if not dec.value:
+        raise SystemExit("decoder_create failed: " + L.last_error())
+    back = torch.empty((H, W, NC), dtype=torch.uint16).pin_memory()       # decoded frame lands here (e2e arm)
+    back_planes = j2k.planes_of(back.numpy())
+    dms = (C.c_float * 8)()
+    tdec = [0.0]
+
     def step_device(i):
+        """encode a frame that is resident in HBM, decode the codestream, leave the pixels in HBM"""
         d = dev[i % NROT]
         rc = lib.j2kcuda_encoder_set_device_input(enc, C.c_void_p(d.data_ptr()), C.c_int64(W * NC * 2), L.USHORT)
         rc = rc or lib.j2kcuda_encoder_run(enc)
         rc = rc or lib.j2kcuda_encoder_finish(enc, C.byref(out), C.byref(n))
+        t0 = time.perf_counter()
+        rc = rc or lib.j2kcuda_decoder_prepare(dec, out, n, 0)
+        rc = rc or lib.j2kcuda_decoder_run(dec)
+        tdec[0] += time.perf_counter() - t0
         if rc:
-            raise SystemExit("encode failed: " + L.last_error())
+            raise SystemExit("step failed: " + L.last_error())
         lib.j2kcuda_free(out)
         return n.value
 
     def step_host(i):
+        """the same through the reference-facing calls with pinned host buffers on both sides"""
         rc = lib.j2kcuda_encoder_upload(enc, planes[i % NROT], NC)
         rc = rc or lib.j2kcuda_encoder_run(enc)
         rc = rc or lib.j2kcuda_encoder_finish(enc, C.byref(out), C.byref(n))
+        t0 = time.perf_counter()
+        rc = rc or lib.j2kcuda_decoder_prepare(dec, out, n, 0)
+        rc = rc or lib.j2kcuda_decoder_run(dec)
+        rc = rc or lib.j2kcuda_decoder_download(dec, back_planes, NC)
+        tdec[0] += time.perf_counter() - t0
         if rc:
-            raise SystemExit("encode failed: " + L.last_error())
+            raise SystemExit("step failed: " + L.last_error())
         lib.j2kcuda_free(out)
         return n.value
 
@@ -181,6 +205,8 @@ def main():
             dist.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         acc = np.zeros(8)
+        dacc = np.zeros(7)
+        tdec[0] = 0.0
         launches = nbytes = d2h = 0
         torch.cuda.synchronize()
         e0.record()
@@ -191,24 +217,31 @@ def main():
             acc += np.array(list(ms))
             launches += cnt[0]
             d2h = cnt[5]
+            lib.j2kcuda_decoder_timings(dec, dms, 7)
+            lib.j2kcuda_decoder_counters(dec, cnt, 6)
+            dacc += np.array(list(dms)[:7])
+            launches += cnt[0]
         e1.record()
         torch.cuda.synchronize()
         t = torch.tensor([e0.elapsed_time(e1)], device="cuda")
         if world > 1:
             dist.barrier()
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item()), acc / args.steps, launches, nbytes / args.steps, d2h
+        return float(t.item()), acc / args.steps, launches, nbytes / args.steps, d2h, dacc / args.steps, tdec[0] / args.steps * 1e3
 
     sampler = ClockSampler(local)
     sampler.start()
-    t_dev, st_dev, launches, cs_bytes, d2h_dev = timed(step_device)
-    t_e2e, st_e2e, _, _, d2h_e2e = timed(step_host)
+    t_dev, st_dev, launches, cs_bytes, d2h_dev, dst_dev, dec_ms_dev = timed(step_device)
+    t_e2e, st_e2e, _, _, d2h_e2e, dst_e2e, dec_ms_e2e = timed(step_host)
+    if not np.array_equal(back.numpy(), host[(args.warmup + args.steps - 1) % NROT].numpy()):
+        raise SystemExit("round trip is not lossless")
     sampler.stop = True
     sampler.join(timeout=3)
 
     lib.j2kcuda_encoder_counters(enc, cnt, 6)
     nblocks, nsym = int(cnt[1]), int(cnt[2])
     lib.j2kcuda_encoder_destroy(enc)
+    lib.j2kcuda_decoder_destroy(dec)
     if rank != 0:
         return
     mpix = W * H / 1e6
@@ -219,19 +252,21 @@ def main():
     l1_ms = float(st_dev[7])
     achieved = l1_bytes / (l1_ms * 1e-3) / 1e9
     line = {
-        "metric": "4K lossless encode MPix/s", "value": value, "unit": "MPix/s", "n_gpus": world, "steps": args.steps,
+        "metric": "4K lossless encode+decode MPix/s", "value": value, "unit": "MPix/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": t_dev / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int32", "data": "synthetic (%s)" % args.kind,
-        "config": {"workload": WORKLOAD, "direction": "encode", "frames_per_step_per_gpu": 1,
+        "config": {"workload": WORKLOAD, "direction": "encode then decode of the same frame (round trip verified lossless)", "frames_per_step_per_gpu": 1,
                    "l2": "inputs and planes larger than L2: %d rotating frames" % NROT,
                    "codestream_bytes_per_frame": cs_bytes, "code_blocks_per_frame": nblocks, "mq_symbols_per_frame": nsym},
-        "e2e": {"value": e2e, "unit": "MPix/s", "h2d_bytes_per_step": W * H * NC * 2, "d2h_bytes_per_step": int(d2h_e2e),
+        "e2e": {"value": e2e, "unit": "MPix/s", "h2d_bytes_per_step": int(W * H * NC * 2 + cs_bytes), "d2h_bytes_per_step": int(d2h_e2e + W * H * NC * 2),
                 "ms_per_step": t_e2e / args.steps},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "k_dwt_forward<Fwd53> level 1", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": l1_bytes, "avg_launch_ms": l1_ms},
         "stages_ms": {k: float(v) for k, v in zip(["upload", "mct", "dwt", "t1_context", "t1_mq", "compact_d2h", "host_t2", "dwt_l1"], st_dev)},
+        "decode_stages_ms": {k: float(v) for k, v in zip(["host_parse", "h2d", "t1", "idwt", "imct_pack", "d2h", "idwt_l1"], dst_dev)},
+        "encode_mpix_s": mpix / ((t_dev / args.steps - dec_ms_dev) * 1e-3), "decode_mpix_s": mpix / (dec_ms_dev * 1e-3),
         "t1": {"code_blocks_per_s": nblocks / ((st_dev[3] + st_dev[4]) * 1e-3), "mq_symbols_per_s": nsym / (st_dev[4] * 1e-3)},
         "clocks": sampler.summary(),
     }
@@ -246,7 +281,7 @@ def main():
             fn(pl)
         dt = (time.perf_counter() - t0) / reps
         line["cpu_baseline"] = {"value": w * h / dt / 1e6, "unit": "MPix/s", "cores": cores, "kind": kind,
-                                "sample": "%d encode(s) of one %dx%d 16-bit RGBA frame, ext/grok CPU encoder" % (reps, w, h)}
+                                "sample": "%d encode+decode round trip(s) of one %dx%d 16-bit RGBA frame, ext/grok on the host cores" % (reps, w, h)}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

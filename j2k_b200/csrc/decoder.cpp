@@ -130,7 +130,7 @@ static int prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned 
     for (auto& t : d->host.tiles)
         for (size_t k = 0; k < t.geo.cblks.size(); ++k)
             if (t.geo.cblks[k].res <= maxres) seg += (((size_t)t.blocks[k].len + 2) + 7) & ~(size_t)7;
-    if (int rc = grow_host(d->h_seg, d->h_seg_cap, seg + 16)) return rc;
+    if (int rc = grow_host(d->h_seg, d->h_seg_cap, seg + 64)) return rc;
     seg = 0;
     d->level_jobs.assign(levels, {});
     uint64_t nblk = 0;
@@ -179,6 +179,8 @@ static int prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned 
             ++nblk;
         }
     }
+    memset(d->h_seg + seg, 0xff, 32);          // the word-wise MQ reader looks up to 24 bytes past a segment
+    seg += 32;
     d->seg_bytes = seg;
     // ---- DWT job tables ----
     std::vector<DwtJob> all;
@@ -465,8 +467,9 @@ int j2kcuda_stage_t1_decode(const uint8_t* data, const int32_t* blk, int nblk, i
         b.coeff = (int32_t*)(uintptr_t)outn;              // patched below once the device buffer exists
         in += (size_t)g[5]; outn += (size_t)g[0] * g[1];
     }
+    arena.insert(arena.end(), 32, 0xff);
     int32_t* d_out = nullptr; uint8_t* d_seg = nullptr; T1DecBlock* d_blk = nullptr;
-    CK(cudaMalloc(&d_out, (outn ? outn : 1) * 4)); CK(cudaMalloc(&d_seg, arena.size() + 8)); CK(cudaMalloc(&d_blk, sizeof(T1DecBlock) * (nblk ? nblk : 1)));
+    CK(cudaMalloc(&d_out, (outn ? outn : 1) * 4)); CK(cudaMalloc(&d_seg, arena.size())); CK(cudaMalloc(&d_blk, sizeof(T1DecBlock) * (nblk ? nblk : 1)));
     for (auto& b : hb) b.coeff = d_out + (uintptr_t)b.coeff;
     CK(cudaMemcpy(d_seg, arena.data(), arena.size(), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(d_blk, hb.data(), sizeof(T1DecBlock) * nblk, cudaMemcpyHostToDevice));

@@ -27,20 +27,32 @@ struct DRows {                // index = row + 1
     u64 sig[66], sgn[66], vis[66], ref[66], bit[66], last[66];
 };
 
+// MQ decoder (mqc.cpp:336-378, 560-595).  The byte stream is consumed through two 8-byte words held in
+// registers; the word after them is fetched when the window slides, i.e. dozens of decisions before
+// any of its bytes is needed.  The segment must start 8-byte aligned, be followed by two 0xFF bytes
+// (which reproduces the reference's behaviour at and past the end of the data, mqc.cpp:336-365) and
+// by at least 24 more readable bytes.
 struct MqDec {
     uint32_t a, c, ct;
-    const uint8_t* bp;        // data is followed by two 0xFF bytes, which reproduces the reference's
-                              // behaviour at and past the end of the segment (mqc.cpp:336-365)
+    const u64* wp;            // next word to fetch
+    u64 w0, w1;               // bytes [8k, 8k+8) and [8k+8, 8k+16) of the segment
+    uint32_t off;             // position of the current byte inside w0
+    J2K_HD inline void advance() {
+        if (++off == 8) { off = 0; w0 = w1; w1 = *wp++; }
+    }
     J2K_HD inline void bytein() {
-        const uint32_t cur = bp[0], nxt = bp[1];
+        const uint32_t cur = (uint32_t)(w0 >> (8 * off)) & 0xffu;
+        const uint32_t nxt = off < 7 ? (uint32_t)(w0 >> (8 * off + 8)) & 0xffu : (uint32_t)w1 & 0xffu;
         if (cur == 0xffu) {
             if (nxt > 0x8fu) { c += 0xff00u; ct = 8; }
-            else { ++bp; c += nxt << 9; ct = 7; }
-        } else { ++bp; c += nxt << 8; ct = 8; }
+            else { advance(); c += nxt << 9; ct = 7; }
+        } else { advance(); c += nxt << 8; ct = 8; }
     }
     J2K_HD void init(const uint8_t* p) {                  // mqc.cpp:560-575
-        bp = p;
-        c = (uint32_t)p[0] << 16;
+        wp = reinterpret_cast<const u64*>(p);
+        w0 = *wp++; w1 = *wp++;
+        off = 0;
+        c = ((uint32_t)w0 & 0xffu) << 16;
         bytein();
         c <<= 7; ct -= 7; a = 0x8000u;
     }
@@ -81,17 +93,23 @@ struct Stripe {               // rows q = 0..5 <-> y = 4*stripe - 1 + q
     u64 V[4], F[4], B[4], L[4];   // visited, refined, this plane's bits, coded in this plane
 };
 
-// zero-coding neighbourhood index of sample (x, row q) from the live significance rows
-J2K_HD inline uint32_t nbhood(const Stripe& s, int q, int x) {
-    const uint32_t up = w3(s.S[q - 1], x), mid = w3(s.S[q], x), dn = w3(s.S[q + 1], x);
-    return up | ((mid & 1u) << 3) | ((mid >> 2) << 4) | (dn << 5);
+// 3-bit significance windows (columns x-1, x, x+1) of the six rows around the stripe, for the column
+// being scanned; kept current as samples of that column become significant
+struct Col { uint32_t s[6]; };
+
+J2K_HD inline void col_load(const Stripe& st, int x, Col& c) {
+#pragma unroll
+    for (int q = 0; q < 6; ++q) c.s[q] = w3(st.S[q], x);
+}
+// zero-coding neighbourhood index: bits 0 NW, 1 N, 2 NE, 3 W, 4 E, 5 SW, 6 S, 7 SE
+J2K_HD inline uint32_t nbhood(const Col& c, int q) {
+    return c.s[q - 1] | ((c.s[q] & 1u) << 3) | ((c.s[q] >> 2) << 4) | (c.s[q + 1] << 5);
 }
 
-J2K_HD inline void decode_sign(Stripe& s, MqDec& mq, uint8_t* st, const uint32_t* tab, const uint8_t* sc, int q, int x) {
-    const uint32_t ms = w3(s.S[q], x), mg = w3(s.G[q], x);
-    const uint32_t sn = (w3(s.S[q - 1], x) >> 1) & 1u, ss = (w3(s.S[q + 1], x) >> 1) & 1u;
+J2K_HD inline void decode_sign(Stripe& s, Col& c, MqDec& mq, uint8_t* st, const uint32_t* tab, const uint8_t* sc, int q, int x) {
+    const uint32_t mg = w3(s.G[q], x);
     const uint32_t gn = (w3(s.G[q - 1], x) >> 1) & 1u, gs = (w3(s.G[q + 1], x) >> 1) & 1u;
-    const uint32_t sw = ms & 1u, se = ms >> 2;
+    const uint32_t sw = c.s[q] & 1u, se = c.s[q] >> 2, sn = (c.s[q - 1] >> 1) & 1u, ss = (c.s[q + 1] >> 1) & 1u;
     const uint32_t idx = sw | (se << 1) | (sn << 2) | (ss << 3) | ((sw & mg) << 4) | ((se & (mg >> 2)) << 5) | ((sn & gn) << 6) | ((ss & gs) << 7);
     const uint32_t e = sc[idx];
     const uint32_t neg = mq.decode(st, tab, CTX_SC + (e & 7u)) ^ (e >> 3);
@@ -99,8 +117,8 @@ J2K_HD inline void decode_sign(Stripe& s, MqDec& mq, uint8_t* st, const uint32_t
     s.G[q] |= (u64)neg << x;
     s.B[q - 1] |= 1ull << x;
     s.L[q - 1] |= 1ull << x;
+    c.s[q] |= 2u;
 }
-
 
 // Decode one code-block.  Called by all `nlanes` lanes of a warp with identical arguments except `lane`;
 // the decision loop runs redundantly on warp-uniform data, the lane index only partitions the
@@ -133,8 +151,8 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, uint8_t* st, co
                 valid[r] = (ib + r < h) ? colmask : 0ull;
             }
             if (passtype == 0) {
-                // significance propagation: columns that have (or acquire) a significant sample in
-                // their 3x6 window
+                // significance propagation: only columns that have (or acquire, from the column just
+                // scanned) a significant sample in their 3x6 window can hold candidates
                 u64 active = 0;
 #pragma unroll
                 for (int q = 0; q < 6; ++q) active |= (s.S[q] << 1) | s.S[q] | (s.S[q] >> 1);
@@ -143,14 +161,16 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, uint8_t* st, co
                 while (u64 rem = active & ~donec) {
                     const int x = J2K_FFSLL(rem) - 1;
                     donec |= 1ull << x;
+                    Col c;
+                    col_load(s, x, c);
 #pragma unroll
                     for (int r = 0; r < 4; ++r) {
                         const int q = r + 1;
-                        if (!((valid[r] >> x) & 1ull) || ((s.S[q] >> x) & 1ull)) continue;
-                        const uint32_t nb = nbhood(s, q, x);
+                        if (!((valid[r] >> x) & 1ull) || (c.s[q] & 2u)) continue;
+                        const uint32_t nb = nbhood(c, q);
                         if (!nb) continue;
                         if (mq.decode(st, mqtab, zc[nb])) {
-                            decode_sign(s, mq, st, mqtab, sc, q, x);
+                            decode_sign(s, c, mq, st, mqtab, sc, q, x);
                             active |= (2ull << x) & colmask;           // the next column may now hold candidates
                         }
                         s.V[r] |= 1ull << x;
@@ -158,58 +178,53 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, uint8_t* st, co
                 }
             } else if (passtype == 1) {
                 // magnitude refinement: significant and not coded in this plane's first pass
-                u64 cols = 0;
+                u64 memb[4], cols = 0;
 #pragma unroll
-                for (int r = 0; r < 4; ++r) cols |= s.S[r + 1] & ~s.V[r] & valid[r];
+                for (int r = 0; r < 4; ++r) { memb[r] = s.S[r + 1] & ~s.V[r] & valid[r]; cols |= memb[r]; }
                 while (cols) {
                     const int x = J2K_FFSLL(cols) - 1;
                     cols &= cols - 1;
+                    Col c;
+                    col_load(s, x, c);
 #pragma unroll
                     for (int r = 0; r < 4; ++r) {
                         const int q = r + 1;
-                        if (!((s.S[q] & ~s.V[r] & valid[r]) >> x & 1ull)) continue;
-                        const uint32_t ctx = ((s.F[r] >> x) & 1ull) ? CTX_MAG + 2 : (nbhood(s, q, x) ? CTX_MAG + 1 : CTX_MAG);
+                        if (!((memb[r] >> x) & 1ull)) continue;
+                        const uint32_t ctx = ((s.F[r] >> x) & 1ull) ? CTX_MAG + 2 : (nbhood(c, q) ? CTX_MAG + 1 : CTX_MAG);
                         const uint32_t bit = mq.decode(st, mqtab, ctx);
                         s.B[r] |= (u64)bit << x;
-                        s.L[r] |= 1ull << x;
-                        s.F[r] |= 1ull << x;
                     }
                 }
+#pragma unroll
+                for (int r = 0; r < 4; ++r) { s.L[r] |= memb[r]; s.F[r] |= memb[r]; }
             } else {
                 // cleanup: everything not yet significant and not visited
-                u64 cols = 0;
+                u64 memb[4], cols = 0;
 #pragma unroll
-                for (int r = 0; r < 4; ++r) cols |= ~s.S[r + 1] & ~s.V[r] & valid[r];
-                const bool fullstripe = ib + 3 < h;
+                for (int r = 0; r < 4; ++r) { memb[r] = ~s.S[r + 1] & ~s.V[r] & valid[r]; cols |= memb[r]; }
+                const u64 memall = (ib + 3 < h) ? (memb[0] & memb[1] & memb[2] & memb[3]) : 0ull;
                 while (cols) {
                     const int x = J2K_FFSLL(cols) - 1;
                     cols &= cols - 1;
+                    Col c;
+                    col_load(s, x, c);
                     int rstart = 0;
                     bool partial = false;
-                    if (fullstripe) {
-                        u64 anyw = 0, memall = ~0ull;
-#pragma unroll
-                        for (int q = 0; q < 6; ++q) anyw |= s.S[q];
-#pragma unroll
-                        for (int r = 0; r < 4; ++r) memall &= ~s.S[r + 1] & ~s.V[r];
-                        const bool agg = ((memall >> x) & 1ull) && w3(anyw, x) == 0;
-                        if (agg) {
-                            if (!mq.decode(st, mqtab, CTX_AGG)) continue;
-                            int runlen = (int)mq.decode(st, mqtab, CTX_UNI);
-                            runlen = (runlen << 1) | (int)mq.decode(st, mqtab, CTX_UNI);
-                            rstart = runlen;
-                            partial = true;
-                        }
+                    if (((memall >> x) & 1ull) && (c.s[0] | c.s[1] | c.s[2] | c.s[3] | c.s[4] | c.s[5]) == 0) {
+                        // run-length mode: the whole column and its neighbourhood are insignificant
+                        if (!mq.decode(st, mqtab, CTX_AGG)) continue;
+                        int runlen = (int)mq.decode(st, mqtab, CTX_UNI);
+                        runlen = (runlen << 1) | (int)mq.decode(st, mqtab, CTX_UNI);
+                        rstart = runlen;
+                        partial = true;
                     }
 #pragma unroll
                     for (int r = 0; r < 4; ++r) {
                         const int q = r + 1;
-                        if (r < rstart) continue;
-                        const bool forced = partial && r == rstart;
-                        if (!forced && !((~s.S[q] & ~s.V[r] & valid[r]) >> x & 1ull)) continue;
+                        if (r < rstart || !((memb[r] >> x) & 1ull)) continue;
                         uint32_t bit = 1;
-                        if (!forced) bit = mq.decode(st, mqtab, zc[nbhood(s, q, x)]);
-                        if (bit) decode_sign(s, mq, st, mqtab, sc, q, x);
+                        if (!(partial && r == rstart)) bit = mq.decode(st, mqtab, zc[nbhood(c, q)]);
+                        if (bit) decode_sign(s, c, mq, st, mqtab, sc, q, x);
                     }
                 }
 #pragma unroll
@@ -227,13 +242,23 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, uint8_t* st, co
         if (++passtype == 3 || passno + 1 == blk.npasses) {
             // fold this plane's decoded bits into the magnitudes kept in the coefficient plane
             const bool plane_done = passtype == 3;
-            for (int y = 0; y < h; ++y) {
-                const u64 b = R.bit[y + 1];
-                if (!b && !firstfold) continue;
+            for (int y0 = 0; y0 < h; y0 += 8) {
                 for (int x = lane; x < w; x += nlanes) {
-                    int32_t* p = out + (size_t)y * blk.pitch + x;
-                    int32_t v = firstfold ? 0 : *p;
-                    *p = v | (int32_t)(((b >> x) & 1ull) << bp);
+                    int32_t v[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const int y = y0 + k;
+                        v[k] = 0;
+                        if (!firstfold && y < h && R.bit[y + 1]) v[k] = out[(size_t)y * blk.pitch + x];
+                    }
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const int y = y0 + k;
+                        if (y >= h) continue;
+                        const u64 b = R.bit[y + 1];
+                        if (!b && !firstfold) continue;
+                        out[(size_t)y * blk.pitch + x] = v[k] | (int32_t)(((b >> x) & 1ull) << bp);
+                    }
                 }
             }
             firstfold = false;

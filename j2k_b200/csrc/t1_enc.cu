@@ -426,7 +426,7 @@ k_t1_mq(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __restr
         const uint8_t* __restrict__ sym_arena, const uint32_t* __restrict__ pass_nsym,
         uint8_t* __restrict__ out_arena, T1Result* __restrict__ results, int lanes) {
     __shared__ uint32_t s_mq[96];
-    __shared__ uint32_t s_ctx[T1_NCTX][MQ_THREADS];
+    __shared__ uint32_t s_ctx[32][MQ_THREADS];
     if (threadIdx.x < 94) s_mq[threadIdx.x] = tab->mq[threadIdx.x];
     __syncthreads();
     const int lane = threadIdx.x & 31;
@@ -439,39 +439,64 @@ k_t1_mq(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __restr
     const T1Block blk = blocks[bi];
     const int t = threadIdx.x;
 #pragma unroll
-    for (int k = 0; k < T1_NCTX; ++k) s_ctx[k][t] = 0;
+    for (int k = 0; k < 32; ++k) s_ctx[k][t] = 0;
     s_ctx[CTX_UNI][t] = 46 * 2; s_ctx[CTX_AGG][t] = 3 * 2; s_ctx[CTX_ZC][t] = 4 * 2;     // t1_opt.cpp:686-690
 
     MqEnc q;
     q.a = 0x8000u; q.c = 0; q.ct = 12; q.nb = -1; q.last = 0;                           // mqc.cpp:406-420
     q.out = out_arena + blk.out_off; q.cap = (int)blk.out_cap; q.overflow = false;
-    const uint32_t* sp = reinterpret_cast<const uint32_t*>(sym_arena + (size_t)blk.sym_off * 16);
+    // The symbol stream is read 16 bytes at a time, one chunk ahead of its use, and the context-state
+    // and probability-table look-ups of symbol i+1 are issued before symbol i is coded, so that the
+    // loop-carried chain is only the interval update itself.
+    const uint4* sp = reinterpret_cast<const uint4*>(sym_arena + (size_t)blk.sym_off * 16);
     const uint32_t* pn = pass_nsym + (size_t)bi * T1_MAX_PASSES;
-    uint32_t pos = 0, word = 0;
-    for (int pass = 0; pass < npasses; ++pass) {
-        const uint32_t n = pn[pass];
-        for (uint32_t i = 0; i < n; ++i, ++pos) {
-            if ((pos & 3u) == 0) word = __ldg(sp + (pos >> 2));
-            const uint32_t s = (word >> ((pos & 3u) * 8)) & 0xffu;
-            const uint32_t ctx = s >> 1, d = s & 1u;
-            const uint32_t st = s_ctx[ctx][t];
-            const uint32_t e = s_mq[st];
-            const uint32_t qe = e & 0xffffu;
+    const uint32_t nsym = res.nsym;
+    int pass = 0;
+    uint32_t pend = pn[0], pos = 0;
+    uint4 nxt = nsym ? __ldg(sp) : make_uint4(0, 0, 0, 0);
+    uint32_t cctx = (nxt.x & 0xffu) >> 1;
+    uint32_t cst = s_ctx[cctx & 31u][t], ce = s_mq[cst];
+    for (uint32_t base = 0; base < nsym; base += 16) {
+        const uint4 cur = nxt;
+        if (base + 16 < nsym) nxt = __ldg(sp + (base >> 4) + 1);
+        const uint32_t w[5] = {cur.x, cur.y, cur.z, cur.w, nxt.x};
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            if (base + k >= nsym) break;
+            while (pass < npasses && pos == pend) {            // t1_opt.cpp:719
+                res.rate[pass] = (q.nb < 0 ? 0 : q.nb) + 3;
+                if (++pass < npasses) pend += pn[pass];
+            }
+            const uint32_t d = (w[k >> 2] >> ((k & 3) * 8)) & 1u;
+            const uint32_t ns = (w[(k + 1) >> 2] >> (((k + 1) & 3) * 8)) & 0xffu;
+            const uint32_t nctx = (ns >> 1) & 31u;
+            uint32_t nst = s_ctx[nctx][t];
+            uint32_t ne = s_mq[nst];
+            const uint32_t qe = ce & 0xffffu;
             q.a -= qe;
-            if (d == (st & 1u)) {                              // MPS, mqc.cpp:271-285
+            uint32_t newst = cst;
+            if (d == (cst & 1u)) {                             // MPS, mqc.cpp:271-285
                 if (q.a & 0x8000u) { q.c += qe; }
                 else {
                     if (q.a < qe) q.a = qe; else q.c += qe;
-                    s_ctx[ctx][t] = (e >> 16) & 0xffu;
-                    q.renorm();
+                    newst = (ce >> 16) & 0xffu;
                 }
             } else {                                           // LPS, mqc.cpp:287-297
                 if (q.a < qe) q.c += qe; else q.a = qe;
-                s_ctx[ctx][t] = e >> 24;
+                newst = ce >> 24;
+            }
+            if (!(q.a & 0x8000u)) {                            // every path that changes the state renormalises
+                s_ctx[cctx][t] = newst;
+                if (nctx == cctx) { nst = newst; ne = s_mq[newst]; }
                 q.renorm();
             }
+            cctx = nctx; cst = nst; ce = ne;
+            ++pos;
         }
-        res.rate[pass] = (q.nb < 0 ? 0 : q.nb) + 3;            // t1_opt.cpp:719
+    }
+    while (pass < npasses) {
+        res.rate[pass] = (q.nb < 0 ? 0 : q.nb) + 3;
+        ++pass;
     }
     // flush, mqc.cpp:299-306, 441-452
     {

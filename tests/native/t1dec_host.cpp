@@ -11,7 +11,8 @@ using namespace j2k::t1dec;
 extern "C" int t1dec_host_block(const uint8_t* data, int len, int w, int h, int orient, int numbps, int npasses,
                                 const uint8_t* zc, const uint8_t* sc, const uint32_t* mq, int32_t* out) {
     std::vector<uint8_t> seg(data, data + len);
-    seg.push_back(0xff); seg.push_back(0xff);
+    for (int i = 0; i < 40; ++i) seg.push_back(0xff);
+    while (reinterpret_cast<uintptr_t>(seg.data()) & 7) return -1;
     T1DecBlock b;
     memset(&b, 0, sizeof(b));
     b.coeff = out; b.pitch = w; b.w = (uint16_t)w; b.h = (uint16_t)h; b.orient = (uint8_t)orient; b.qmfbid = 1;
