@@ -22,10 +22,10 @@ k_t1_decode(const T1DecBlock* __restrict__ blocks, int nblocks, const T1Tables* 
             const uint8_t* __restrict__ seg_arena, int raw_output) {
     __shared__ DRows s_rows[DEC_WARPS];
     __shared__ uint8_t s_state[DEC_WARPS][32];
-    __shared__ uint8_t s_zc[4 * 256];
+    __shared__ uint8_t s_zc[4 * 512];
     __shared__ uint8_t s_sc[256];
     __shared__ uint32_t s_mq[96];
-    for (int i = threadIdx.x; i < 1024; i += blockDim.x) s_zc[i] = tab->zc[i];
+    for (int i = threadIdx.x; i < 2048; i += blockDim.x) s_zc[i] = tab->zc9[i];
     for (int i = threadIdx.x; i < 256; i += blockDim.x) s_sc[i] = tab->sc[i];
     if (threadIdx.x < 94) s_mq[threadIdx.x] = tab->mq[threadIdx.x];
     __syncthreads();

@@ -12,7 +12,9 @@
 #define J2K_FFSLL(v) __ffsll((long long)(v))
 #define J2K_SYNCWARP() __syncwarp()
 #define J2K_FMUL(a, b) __fmul_rn((a), (b))
+#define J2K_NOINLINE __noinline__
 #else
+#define J2K_NOINLINE
 #define J2K_FFSLL(v) __builtin_ffsll((long long)(v))
 #define J2K_SYNCWARP() ((void)0)
 #define J2K_FMUL(a, b) ((a) * (b))
@@ -63,6 +65,8 @@ struct MqDec {
         } while (a < 0x8000u);
     }
     // st: per-context state (index*2 + mps), tab: T1Tables::mq
+    // (kept out of line on the device: the decision loop has a dozen call sites and must stay inside
+    // the instruction cache)
     J2K_HD inline uint32_t decode(uint8_t* st, const uint32_t* tab, uint32_t ctx) {   // mqc.cpp:577-595
         const uint32_t s = st[ctx], e = tab[s], qe = e & 0xffffu;
         uint32_t d = s & 1u;
@@ -93,31 +97,33 @@ struct Stripe {               // rows q = 0..5 <-> y = 4*stripe - 1 + q
     u64 V[4], F[4], B[4], L[4];   // visited, refined, this plane's bits, coded in this plane
 };
 
-// 3-bit significance windows (columns x-1, x, x+1) of the six rows around the stripe, for the column
-// being scanned; kept current as samples of that column become significant
-struct Col { uint32_t s[6]; };
-
-J2K_HD inline void col_load(const Stripe& st, int x, Col& c) {
+// The column being scanned is worked on in packed form so that the row loop can stay rolled (one copy
+// of the MQ decoder per call site keeps the kernel inside the instruction cache):
+//   win / gwin  3-bit windows (columns x-1, x, x+1) of the six rows around the stripe, row q at bits
+//               3q..3q+2, for significance and sign; the 9 bits starting at 3(q-1) are the 3x3
+//               neighbourhood of the sample in row q (the layout the reference's packed flags use,
+//               t1_opt.h:57-168), which indexes the zero-coding table directly
+//   nibbles     one bit per stripe row
+J2K_HD inline uint32_t pack_win(const u64* rows, int x) {
+    uint32_t w = 0;
 #pragma unroll
-    for (int q = 0; q < 6; ++q) c.s[q] = w3(st.S[q], x);
+    for (int q = 0; q < 6; ++q) w |= w3(rows[q], x) << (3 * q);
+    return w;
 }
-// zero-coding neighbourhood index: bits 0 NW, 1 N, 2 NE, 3 W, 4 E, 5 SW, 6 S, 7 SE
-J2K_HD inline uint32_t nbhood(const Col& c, int q) {
-    return c.s[q - 1] | ((c.s[q] & 1u) << 3) | ((c.s[q] >> 2) << 4) | (c.s[q + 1] << 5);
+J2K_HD inline uint32_t nibble(const u64* rows, int x) {
+    return (uint32_t)((rows[0] >> x) & 1ull) | ((uint32_t)((rows[1] >> x) & 1ull) << 1) |
+           ((uint32_t)((rows[2] >> x) & 1ull) << 2) | ((uint32_t)((rows[3] >> x) & 1ull) << 3);
+}
+J2K_HD inline void scatter(u64* rows, uint32_t nib, int x) {
+#pragma unroll
+    for (int r = 0; r < 4; ++r) rows[r] |= (u64)((nib >> r) & 1u) << x;
 }
 
-J2K_HD inline void decode_sign(Stripe& s, Col& c, MqDec& mq, uint8_t* st, const uint32_t* tab, const uint8_t* sc, int q, int x) {
-    const uint32_t mg = w3(s.G[q], x);
-    const uint32_t gn = (w3(s.G[q - 1], x) >> 1) & 1u, gs = (w3(s.G[q + 1], x) >> 1) & 1u;
-    const uint32_t sw = c.s[q] & 1u, se = c.s[q] >> 2, sn = (c.s[q - 1] >> 1) & 1u, ss = (c.s[q + 1] >> 1) & 1u;
-    const uint32_t idx = sw | (se << 1) | (sn << 2) | (ss << 3) | ((sw & mg) << 4) | ((se & (mg >> 2)) << 5) | ((sn & gn) << 6) | ((ss & gs) << 7);
-    const uint32_t e = sc[idx];
-    const uint32_t neg = mq.decode(st, tab, CTX_SC + (e & 7u)) ^ (e >> 3);
-    s.S[q] |= 1ull << x;
-    s.G[q] |= (u64)neg << x;
-    s.B[q - 1] |= 1ull << x;
-    s.L[q - 1] |= 1ull << x;
-    c.s[q] |= 2u;
+// sign-coding table index from the 9-bit significance and sign neighbourhoods (bits 1 N, 3 W, 5 E, 7 S)
+J2K_HD inline uint32_t sc_index(uint32_t s9, uint32_t g9) {
+    g9 &= s9;
+    return ((s9 >> 3) & 1u) | (((s9 >> 5) & 1u) << 1) | (((s9 >> 1) & 1u) << 2) | (((s9 >> 7) & 1u) << 3) |
+           (((g9 >> 3) & 1u) << 4) | (((g9 >> 5) & 1u) << 5) | (((g9 >> 1) & 1u) << 6) | (((g9 >> 7) & 1u) << 7);
 }
 
 // Decode one code-block.  Called by all `nlanes` lanes of a warp with identical arguments except `lane`;
@@ -127,7 +133,7 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, uint8_t* st, co
                                 const uint32_t* mqtab, const uint8_t* seg_arena, int raw_output, int lane, int nlanes) {
     const int w = blk.w, h = blk.h;
     int32_t* out = blk.coeff;
-    const uint8_t* zc = zc_all + blk.orient * 256;
+    const uint8_t* zc = zc_all + blk.orient * 512;
     const int nstripes = (h + 3) >> 2;
     const u64 colmask = w == 64 ? ~0ull : ((1ull << w) - 1);
 
@@ -161,19 +167,27 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, uint8_t* st, co
                 while (u64 rem = active & ~donec) {
                     const int x = J2K_FFSLL(rem) - 1;
                     donec |= 1ull << x;
-                    Col c;
-                    col_load(s, x, c);
-#pragma unroll
+                    uint32_t win = pack_win(s.S, x), gwin = 0;
+                    bool have_g = false;
+                    const uint32_t val4 = nibble(valid, x);
+                    uint32_t new4 = 0, neg4 = 0, vis4 = 0;
+#pragma unroll 1
                     for (int r = 0; r < 4; ++r) {
-                        const int q = r + 1;
-                        if (!((valid[r] >> x) & 1ull) || (c.s[q] & 2u)) continue;
-                        const uint32_t nb = nbhood(c, q);
-                        if (!nb) continue;
-                        if (mq.decode(st, mqtab, zc[nb])) {
-                            decode_sign(s, c, mq, st, mqtab, sc, q, x);
-                            active |= (2ull << x) & colmask;           // the next column may now hold candidates
-                        }
-                        s.V[r] |= 1ull << x;
+                        const uint32_t s9 = (win >> (3 * r)) & 0x1ffu;
+                        if (!((val4 >> r) & 1u) || (s9 & 0x10u) || !(s9 & 0x1efu)) continue;
+                        vis4 |= 1u << r;
+                        if (!mq.decode(st, mqtab, zc[s9 & 0x1efu])) continue;
+                        if (!have_g) { gwin = pack_win(s.G, x); have_g = true; }
+                        const uint32_t e = sc[sc_index(s9, (gwin >> (3 * r)) & 0x1ffu)];
+                        const uint32_t neg = mq.decode(st, mqtab, CTX_SC + (e & 7u)) ^ (e >> 3);
+                        win |= 2u << (3 * r + 3);
+                        gwin |= (neg << 1) << (3 * r + 3);
+                        new4 |= 1u << r; neg4 |= neg << r;
+                    }
+                    if (vis4) scatter(s.V, vis4, x);
+                    if (new4) {
+                        scatter(s.S + 1, new4, x); scatter(s.G + 1, neg4, x); scatter(s.B, new4, x); scatter(s.L, new4, x);
+                        active |= (2ull << x) & colmask;               // the next column may now hold candidates
                     }
                 }
             } else if (passtype == 1) {
@@ -184,16 +198,17 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, uint8_t* st, co
                 while (cols) {
                     const int x = J2K_FFSLL(cols) - 1;
                     cols &= cols - 1;
-                    Col c;
-                    col_load(s, x, c);
-#pragma unroll
+                    const uint32_t win = pack_win(s.S, x);
+                    const uint32_t mem4 = nibble(memb, x), ref4 = nibble(s.F, x);
+                    uint32_t bit4 = 0;
+#pragma unroll 1
                     for (int r = 0; r < 4; ++r) {
-                        const int q = r + 1;
-                        if (!((memb[r] >> x) & 1ull)) continue;
-                        const uint32_t ctx = ((s.F[r] >> x) & 1ull) ? CTX_MAG + 2 : (nbhood(c, q) ? CTX_MAG + 1 : CTX_MAG);
-                        const uint32_t bit = mq.decode(st, mqtab, ctx);
-                        s.B[r] |= (u64)bit << x;
+                        if (!((mem4 >> r) & 1u)) continue;
+                        const uint32_t s9 = (win >> (3 * r)) & 0x1efu;
+                        const uint32_t ctx = ((ref4 >> r) & 1u) ? CTX_MAG + 2 : (s9 ? CTX_MAG + 1 : CTX_MAG);
+                        bit4 |= mq.decode(st, mqtab, ctx) << r;
                     }
+                    if (bit4) scatter(s.B, bit4, x);
                 }
 #pragma unroll
                 for (int r = 0; r < 4; ++r) { s.L[r] |= memb[r]; s.F[r] |= memb[r]; }
@@ -206,26 +221,33 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, uint8_t* st, co
                 while (cols) {
                     const int x = J2K_FFSLL(cols) - 1;
                     cols &= cols - 1;
-                    Col c;
-                    col_load(s, x, c);
+                    uint32_t win = pack_win(s.S, x), gwin = 0;
+                    bool have_g = false;
+                    const uint32_t mem4 = nibble(memb, x);
                     int rstart = 0;
                     bool partial = false;
-                    if (((memall >> x) & 1ull) && (c.s[0] | c.s[1] | c.s[2] | c.s[3] | c.s[4] | c.s[5]) == 0) {
+                    if (((memall >> x) & 1ull) && win == 0) {
                         // run-length mode: the whole column and its neighbourhood are insignificant
                         if (!mq.decode(st, mqtab, CTX_AGG)) continue;
-                        int runlen = (int)mq.decode(st, mqtab, CTX_UNI);
-                        runlen = (runlen << 1) | (int)mq.decode(st, mqtab, CTX_UNI);
-                        rstart = runlen;
+                        rstart = (int)mq.decode(st, mqtab, CTX_UNI);
+                        rstart = (rstart << 1) | (int)mq.decode(st, mqtab, CTX_UNI);
                         partial = true;
                     }
-#pragma unroll
-                    for (int r = 0; r < 4; ++r) {
-                        const int q = r + 1;
-                        if (r < rstart || !((memb[r] >> x) & 1ull)) continue;
-                        uint32_t bit = 1;
-                        if (!(partial && r == rstart)) bit = mq.decode(st, mqtab, zc[nbhood(c, q)]);
-                        if (bit) decode_sign(s, c, mq, st, mqtab, sc, q, x);
+                    uint32_t new4 = 0, neg4 = 0;
+#pragma unroll 1
+                    for (int r = rstart; r < 4; ++r) {
+                        if (!((mem4 >> r) & 1u)) continue;
+                        const uint32_t s9 = (win >> (3 * r)) & 0x1ffu;
+                        if (partial) partial = false;                  // the sample that ended the run is significant
+                        else if (!mq.decode(st, mqtab, zc[s9 & 0x1efu])) continue;
+                        if (!have_g) { gwin = pack_win(s.G, x); have_g = true; }
+                        const uint32_t e = sc[sc_index(s9, (gwin >> (3 * r)) & 0x1ffu)];
+                        const uint32_t neg = mq.decode(st, mqtab, CTX_SC + (e & 7u)) ^ (e >> 3);
+                        win |= 2u << (3 * r + 3);
+                        gwin |= (neg << 1) << (3 * r + 3);
+                        new4 |= 1u << r; neg4 |= neg << r;
                     }
+                    if (new4) { scatter(s.S + 1, new4, x); scatter(s.G + 1, neg4, x); scatter(s.B, new4, x); scatter(s.L, new4, x); }
                 }
 #pragma unroll
                 for (int r = 0; r < 4; ++r) s.V[r] = 0;

@@ -59,6 +59,13 @@ T1Tables build() {
             int d = (nb & 1) + ((nb >> 2) & 1) + ((nb >> 5) & 1) + ((nb >> 7) & 1);
             t.zc[orient * 256 + nb] = (uint8_t)(CTX_ZC + zc_rule(orient, h, v, d));
         }
+    for (int orient = 0; orient < 4; ++orient)
+        for (int n = 0; n < 512; ++n) {
+            int h = ((n >> 3) & 1) + ((n >> 5) & 1);
+            int v = ((n >> 1) & 1) + ((n >> 7) & 1);
+            int d = (n & 1) + ((n >> 2) & 1) + ((n >> 6) & 1) + ((n >> 8) & 1);
+            t.zc9[orient * 512 + n] = (uint8_t)(CTX_ZC + zc_rule(orient, h, v, d));
+        }
     for (int i = 0; i < 256; ++i) {
         auto contrib = [&](int sigbit, int negbit) { return ((i >> sigbit) & 1) ? (((i >> negbit) & 1) ? -1 : 1) : 0; };
         int hc = contrib(0, 4) + contrib(1, 5), vc = contrib(2, 6) + contrib(3, 7);

@@ -20,6 +20,9 @@ struct T1Tables {
     // (next values are again state*2 + mps, the LPS one with the switch applied)
     uint32_t mq[94];
     uint32_t pad[2];
+    // zero-coding context from the full 3x3 neighbourhood: index = orient*512 + n9, n9 bits: 0 NW, 1 N, 2 NE,
+    // 3 W, 4 centre (ignored), 5 E, 6 SW, 7 S, 8 SE (same idea as lut_ctxno_zc_opt, t1_luts.h)
+    uint8_t zc9[4 * 512];
 };
 
 const T1Tables* t1_tables_device();     // device pointer (valid after device_tables_init)

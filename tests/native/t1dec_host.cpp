@@ -9,7 +9,7 @@ using namespace j2k;
 using namespace j2k::t1dec;
 
 extern "C" int t1dec_host_block(const uint8_t* data, int len, int w, int h, int orient, int numbps, int npasses,
-                                const uint8_t* zc, const uint8_t* sc, const uint32_t* mq, int32_t* out) {
+                                const uint8_t* zc9, const uint8_t* sc, const uint32_t* mq, int32_t* out) {
     std::vector<uint8_t> seg(data, data + len);
     for (int i = 0; i < 40; ++i) seg.push_back(0xff);
     while (reinterpret_cast<uintptr_t>(seg.data()) & 7) return -1;
@@ -23,6 +23,6 @@ extern "C" int t1dec_host_block(const uint8_t* data, int len, int w, int h, int 
     memset(&R, 0, sizeof(R));
     uint8_t st[32] = {0};
     st[CTX_UNI] = 46 * 2; st[CTX_AGG] = 3 * 2; st[CTX_ZC] = 4 * 2;
-    decode_block(b, R, st, zc, sc, mq, seg.data(), 1, 0, 1);
+    decode_block(b, R, st, zc9, sc, mq, seg.data(), 1, 0, 1);
     return 0;
 }

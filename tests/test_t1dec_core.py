@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 
 class Tables(C.Structure):
     _fields_ = [("zc", C.c_uint8 * 1024), ("sc", C.c_uint8 * 256), ("nm", C.c_int16 * 512), ("mq", C.c_uint32 * 94),
-                ("pad", C.c_uint32 * 2)]
+                ("pad", C.c_uint32 * 2), ("zc9", C.c_uint8 * 2048)]
 
 
 @pytest.fixture(scope="module")
@@ -28,7 +28,7 @@ def run(core, data, w, h, orient, numbps, npasses):
     lib, tab = core
     out = np.zeros((h, w), np.int32)
     buf = np.frombuffer(data + b"\0", dtype=np.uint8).copy()
-    lib.t1dec_host_block(buf.ctypes.data_as(C.c_void_p), len(data), w, h, orient, numbps, npasses, tab.zc, tab.sc, tab.mq,
+    lib.t1dec_host_block(buf.ctypes.data_as(C.c_void_p), len(data), w, h, orient, numbps, npasses, tab.zc9, tab.sc, tab.mq,
                          out.ctypes.data_as(C.c_void_p))
     return out
 
