@@ -10,6 +10,7 @@
 // Reference behaviour: t1.cpp:1337-1448 (block loop), :382-584 (significance), :616-806
 // (refinement), :845-1112 (cleanup), mqc.cpp:336-378, 560-595 (MQ decoder).  cblksty == 0 only.
 #include "t1_dec_core.cuh"
+#include <cstdlib>
 
 namespace j2k {
 namespace {
@@ -17,7 +18,8 @@ namespace {
 using namespace t1dec;
 constexpr int DEC_WARPS = 4;
 
-__global__ void __launch_bounds__(32 * DEC_WARPS)
+template <int MINB>
+__global__ void __launch_bounds__(32 * DEC_WARPS, MINB)
 k_t1_decode(const T1DecBlock* __restrict__ blocks, int nblocks, const T1Tables* __restrict__ tab,
             const uint8_t* __restrict__ seg_arena, int raw_output) {
     __shared__ DRows s_rows[DEC_WARPS];
@@ -54,7 +56,12 @@ k_t1_decode(const T1DecBlock* __restrict__ blocks, int nblocks, const T1Tables* 
 
 void launch_t1_decode(const T1DecBlock* d_blocks, int nblocks, const uint8_t* seg_arena, int raw_output, cudaStream_t st) {
     if (nblocks <= 0) return;
-    k_t1_decode<<<(nblocks + DEC_WARPS - 1) / DEC_WARPS, 32 * DEC_WARPS, 0, st>>>(d_blocks, nblocks, t1_tables_device(), seg_arena, raw_output);
+    // register budget / occupancy trade-off, tunable for experiments: 4 -> 128 regs, 5 -> 96, 6 -> 80
+    static const int variant = [] { const char* e = getenv("J2KCUDA_DEC_MINB"); return e ? atoi(e) : 4; }();
+    const dim3 grid((nblocks + DEC_WARPS - 1) / DEC_WARPS), block(32 * DEC_WARPS);
+    if (variant <= 4) k_t1_decode<4><<<grid, block, 0, st>>>(d_blocks, nblocks, t1_tables_device(), seg_arena, raw_output);
+    else if (variant == 5) k_t1_decode<5><<<grid, block, 0, st>>>(d_blocks, nblocks, t1_tables_device(), seg_arena, raw_output);
+    else k_t1_decode<6><<<grid, block, 0, st>>>(d_blocks, nblocks, t1_tables_device(), seg_arena, raw_output);
 }
 
 }  // namespace j2k
