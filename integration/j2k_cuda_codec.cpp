@@ -1,0 +1,141 @@
+// See j2k_cuda_codec.h.  Translates j2k::Buffer / FileInfo / InputFile / OutputFile to the plain-C calls of
+// include/j2kcuda.h and throws j2k::Exception on a non-zero status, the way OpenJPEGCodec reports opj_*
+// failures (src/common/j2k_openjpeg_codec.cpp:452-758).
+#include "j2k_cuda_codec.h"
+#include "j2k_exception.h"
+#include "j2kcuda.h"
+
+#include <vector>
+#include <string>
+
+namespace j2k
+{
+
+static std::vector<uint8_t> ReadAll(InputFile &file)
+{
+	const size_t n = file.FileSize();
+	std::vector<uint8_t> bytes(n);
+	file.Seek(0);
+	if(n && file.Read(&bytes[0], n) != n)
+		throw Exception("Error reading file.");
+	return bytes;
+}
+
+static void Check(int status)
+{
+	if(status != J2KCUDA_OK)
+		throw Exception(std::string("libj2kcuda: ") + j2kcuda_last_error());
+}
+
+static void ToPlanes(const Buffer &buffer, j2kcuda_plane planes[J2K_CODEC_MAX_CHANNELS])
+{
+	for(int i=0; i < buffer.channels; i++)
+	{
+		const Channel &c = buffer.channel[i];
+		planes[i].buf = c.buf;
+		planes[i].colbytes = c.colbytes;
+		planes[i].rowbytes = c.rowbytes;
+		planes[i].width = c.width;
+		planes[i].height = c.height;
+		planes[i].sample_type = (c.sampleType == UCHAR ? J2KCUDA_UCHAR : c.sampleType == USHORT ? J2KCUDA_USHORT :
+									c.sampleType == UINT ? J2KCUDA_UINT : J2KCUDA_INT);
+		planes[i].depth = c.depth;
+		planes[i].sgnd = c.sgnd;
+		planes[i].reserved = 0;
+	}
+}
+
+void CudaCodec::GetFileInfo(InputFile &file, FileInfo &info)
+{
+	const std::vector<uint8_t> bytes = ReadAll(file);
+	j2kcuda_info hdr;
+	Check( j2kcuda_probe(bytes.empty() ? NULL : &bytes[0], bytes.size(), &hdr) );
+
+	// same fields OpenJPEGCodec::GetFileInfo fills from opj_read_header_ex (j2k_openjpeg_codec.cpp:222-429)
+	info.width = hdr.width;
+	info.height = hdr.height;
+	info.channels = hdr.ncomp;
+	info.depth = hdr.prec[0];
+	for(unsigned int i=0; i < hdr.ncomp && i < J2K_CODEC_MAX_CHANNELS; i++)
+		info.subsampling[i] = Subsampling(hdr.dx[i], hdr.dy[i]);
+	info.format = (hdr.is_jp2 ? JP2 : J2C);
+	info.colorSpace = (hdr.ncomp >= 3 ? sRGB : sLUM);
+	info.alpha = (hdr.ncomp == 2 || hdr.ncomp == 4 ? STRAIGHT : NO_ALPHA);
+	info.settings.reversible = hdr.reversible;
+	info.settings.layers = hdr.numlayers;
+	info.settings.tileSize = (hdr.tiles_x * hdr.tiles_y > 1 ? hdr.tile_w : 0);
+}
+
+void CudaCodec::ReadFile(InputFile &file, const Buffer &buffer, unsigned int subsample, Progress *progress)
+{
+	const std::vector<uint8_t> bytes = ReadAll(file);
+	unsigned int reduce = 0;                     // cp_reduce = log2(subsample), j2k_openjpeg_codec.cpp:496-501
+	while((1u << (reduce + 1)) <= subsample)
+		reduce++;
+
+	j2kcuda_plane planes[J2K_CODEC_MAX_CHANNELS];
+	ToPlanes(buffer, planes);
+
+	Check( j2kcuda_decode(bytes.empty() ? NULL : &bytes[0], bytes.size(), reduce, planes, buffer.channels, NULL, NULL) );
+
+	if(progress && progress->abortProc && progress->abortProc(progress->refCon))   // polled once, as the reference does (:515-528)
+		progress->keepGoing = false;
+}
+
+void CudaCodec::WriteFile(OutputFile &file, const FileInfo &info, const Buffer &buffer, Progress *progress)
+{
+	j2kcuda_params p;
+	j2kcuda_default_params(&p);
+	p.width = info.width;
+	p.height = info.height;
+	p.ncomp = buffer.channels;
+	p.prec = info.depth;
+	p.sgnd = 0;
+	p.mct = (buffer.channels >= 3 ? 1 : 0);      // what opj_compress does for RGB (bin/jp2/opj_compress.cpp:1399-1400)
+
+	const CompressionSettings &s = info.settings;
+	p.numlayers = (s.method == LOSSLESS ? 1 : s.layers);
+	if(s.tileSize && (s.tileSize < info.width || s.tileSize < info.height))
+		p.tile_w = p.tile_h = s.tileSize;
+	p.prog_order = (s.order == LRCP ? J2KCUDA_LRCP : s.order == RLCP ? J2KCUDA_RLCP : s.order == RPCL ? J2KCUDA_RPCL :
+					s.order == PCRL ? J2KCUDA_PCRL : J2KCUDA_CPRL);
+
+	if(s.method == CINEMA)
+	{
+		p.profile = (s.dciProfile == DCI_4K ? J2KCUDA_PROFILE_CINEMA_4K : J2KCUDA_PROFILE_CINEMA_2K);
+		p.max_cs_size = s.fileSize * 1024;        // the caller pre-computes KiB per frame (src/aftereffects/j2k.cpp:817-830)
+	}
+	else if(s.method == SIZE)
+	{
+		p.irreversible = !s.reversible;
+		const double raw = (double)info.width * info.height * buffer.channels * info.depth / 8.0;
+		p.rates[p.numlayers - 1] = raw / ((double)s.fileSize * 1024.0);
+		for(int i = (int)p.numlayers - 2; i >= 0; i--)
+			p.rates[i] = p.rates[i + 1] * 2.0;
+	}
+	else if(s.method == QUALITY)
+	{
+		p.irreversible = !s.reversible;
+		p.rates[p.numlayers - 1] = 1.0 + (100 - s.quality) * 0.5;   // quality slider -> compression ratio
+		for(int i = (int)p.numlayers - 2; i >= 0; i--)
+			p.rates[i] = p.rates[i + 1] * 2.0;
+	}
+
+	j2kcuda_plane planes[J2K_CODEC_MAX_CHANNELS];
+	ToPlanes(buffer, planes);
+
+	uint8_t *out = NULL;
+	size_t out_len = 0;
+	Check( j2kcuda_encode(&p, planes, buffer.channels, &out, &out_len) );
+
+	const size_t written = file.Write(out, out_len);      // one contiguous codestream, one Write
+	j2kcuda_free(out);
+
+	if(written != out_len)
+		throw Exception("Error writing file.");
+
+	if(progress && progress->abortProc && progress->abortProc(progress->refCon))
+		progress->keepGoing = false;
+}
+
+}; // namespace j2k
