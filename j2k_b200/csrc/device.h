@@ -57,6 +57,8 @@ struct DwtJob {
     int pitch;        // samples, same for src and dst
     int strip0;       // row pairs per segment chosen by dwt_plan_jobs
     int nstrips, nsegs;
+    int strip_cols;   // columns per warp strip (multiple of the columns one lane holds), set by dwt_plan_jobs
+    int pad;
 };
 enum { DWT_53 = 0, DWT_97_FIX = 1, DWT_97_FLOAT = 2 };
 // host-side helper: fills strip/segment counts (jobs[i].strip0 = row pairs per segment, the same

@@ -13,11 +13,11 @@
 // Order of the two directions follows the reference: forward = vertical then horizontal
 // (dwt.cpp:420-506), inverse = horizontal then vertical (dwt.cpp:615-704, 927-1062).
 #include "device.h"
+#include <cstdlib>
 
 namespace j2k {
 namespace {
 
-constexpr int STRIP_COLS = 120;
 constexpr int WARPS_PER_CTA = 4;
 
 __device__ __forceinline__ int mirror(int i, int lo, int hi) {
@@ -33,22 +33,24 @@ __device__ __forceinline__ int fm(int a, int b) {          // opj_intmath.h:255-
     return (int)(((long long)a * (long long)b + 4096) >> 13);
 }
 
-template <typename T> struct Q { T v[4]; };
+// N adjacent samples of one row held by one lane (N = 4 or 8; v[0] sits on an even column)
+template <typename T, int N> struct Q { T v[N]; };
 
 // ---- lifting kernels (forward) -----------------------------------------------------------------
 // Each provides: vertical streaming step (new odd row xo = x(n-1), new even row xe = x(n); emits
 // the finished pair lo = row n-LAG, hi = row n-LAG+1) and the horizontal lifting across lanes.
-struct Fwd53 {
+template <int N> struct Fwd53 {
+    typedef int T;
     static constexpr int LAG = 2, WARM = 1;
-    Q<int> xprev, dprev;      // x(n-2), d(n-3)
-    __device__ void init(const Q<int>& x) {
+    Q<int, N> xprev, dprev;      // x(n-2), d(n-3)
+    __device__ void init(const Q<int, N>& x) {
         xprev = x;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) dprev.v[k] = 0;
+        for (int k = 0; k < N; ++k) dprev.v[k] = 0;
     }
-    __device__ void step(const Q<int>& xo, const Q<int>& xe, Q<int>& lo, Q<int>& hi) {
+    __device__ void step(const Q<int, N>& xo, const Q<int, N>& xe, Q<int, N>& lo, Q<int, N>& hi) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < N; ++k) {
             int d = xo.v[k] - ((xprev.v[k] + xe.v[k]) >> 1);
             lo.v[k] = xprev.v[k] + ((dprev.v[k] + d + 2) >> 2);
             hi.v[k] = d;
@@ -56,28 +58,29 @@ struct Fwd53 {
             xprev.v[k] = xe.v[k];
         }
     }
-    static __device__ void horizontal(Q<int>& r) {
-        int nx = __shfl_down_sync(0xffffffffu, r.v[0], 1);
-        r.v[1] -= (r.v[0] + r.v[2]) >> 1;
-        r.v[3] -= (r.v[2] + nx) >> 1;
-        int pv = __shfl_up_sync(0xffffffffu, r.v[3], 1);
-        r.v[0] += (pv + r.v[1] + 2) >> 2;
-        r.v[2] += (r.v[1] + r.v[3] + 2) >> 2;
+    static __device__ void horizontal(Q<int, N>& r) {
+        const int nx = __shfl_down_sync(0xffffffffu, r.v[0], 1);
+#pragma unroll
+        for (int k = 1; k < N; k += 2) r.v[k] -= (r.v[k - 1] + (k + 1 < N ? r.v[k + 1 < N ? k + 1 : 0] : nx)) >> 1;
+        const int pv = __shfl_up_sync(0xffffffffu, r.v[N - 1], 1);
+#pragma unroll
+        for (int k = 0; k < N; k += 2) r.v[k] += ((k ? r.v[k ? k - 1 : 0] : pv) + r.v[k + 1] + 2) >> 2;
     }
     static __device__ int single(int x, int odd) { return odd ? x * 2 : x; }   // dwt.cpp:318,323
 };
 
-struct Fwd97 {                 // Q13 fixed point, dwt.cpp:365-399
+template <int N> struct Fwd97 {                 // Q13 fixed point, dwt.cpp:365-399
+    typedef int T;
     static constexpr int LAG = 4, WARM = 3;
-    Q<int> x2, d1, s1, d2;     // x(n-2), d1(n-3), s1(n-4), d2(n-5)
-    __device__ void init(const Q<int>& x) {
+    Q<int, N> x2, d1, s1, d2;     // x(n-2), d1(n-3), s1(n-4), d2(n-5)
+    __device__ void init(const Q<int, N>& x) {
         x2 = x;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) d1.v[k] = s1.v[k] = d2.v[k] = 0;
+        for (int k = 0; k < N; ++k) d1.v[k] = s1.v[k] = d2.v[k] = 0;
     }
-    __device__ void step(const Q<int>& xo, const Q<int>& xe, Q<int>& lo, Q<int>& hi) {
+    __device__ void step(const Q<int, N>& xo, const Q<int, N>& xe, Q<int, N>& lo, Q<int, N>& hi) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < N; ++k) {
             int nd1 = xo.v[k] - fm(x2.v[k] + xe.v[k], 12993);
             int ns1 = x2.v[k] - fm(d1.v[k] + nd1, 434);
             int nd2 = d1.v[k] + fm(s1.v[k] + ns1, 7233);
@@ -87,22 +90,26 @@ struct Fwd97 {                 // Q13 fixed point, dwt.cpp:365-399
             x2.v[k] = xe.v[k]; d1.v[k] = nd1; s1.v[k] = ns1; d2.v[k] = nd2;
         }
     }
-    static __device__ void horizontal(Q<int>& r) {
+    // one lifting step on the odd (ODD = 1) or even samples: r[k] += sign * fm(r[k-1] + r[k+1], c)
+    template <int ODD> static __device__ __forceinline__ void lift(Q<int, N>& r, int c, int sign) {
         const unsigned m = 0xffffffffu;
-        int nx = __shfl_down_sync(m, r.v[0], 1);
-        r.v[1] -= fm(r.v[0] + r.v[2], 12993);
-        r.v[3] -= fm(r.v[2] + nx, 12993);
-        int pv = __shfl_up_sync(m, r.v[3], 1);
-        r.v[0] -= fm(pv + r.v[1], 434);
-        r.v[2] -= fm(r.v[1] + r.v[3], 434);
-        nx = __shfl_down_sync(m, r.v[0], 1);
-        r.v[1] += fm(r.v[0] + r.v[2], 7233);
-        r.v[3] += fm(r.v[2] + nx, 7233);
-        pv = __shfl_up_sync(m, r.v[3], 1);
-        r.v[0] += fm(pv + r.v[1], 3633);
-        r.v[2] += fm(r.v[1] + r.v[3], 3633);
-        r.v[0] = fm(r.v[0], 6659); r.v[2] = fm(r.v[2], 6659);
-        r.v[1] = fm(r.v[1], 5038); r.v[3] = fm(r.v[3], 5038);
+        if (ODD) {
+            const int nx = __shfl_down_sync(m, r.v[0], 1);
+#pragma unroll
+            for (int k = 1; k < N; k += 2) r.v[k] += sign * fm(r.v[k - 1] + (k + 1 < N ? r.v[k + 1 < N ? k + 1 : 0] : nx), c);
+        } else {
+            const int pv = __shfl_up_sync(m, r.v[N - 1], 1);
+#pragma unroll
+            for (int k = 0; k < N; k += 2) r.v[k] += sign * fm((k ? r.v[k ? k - 1 : 0] : pv) + r.v[k + 1], c);
+        }
+    }
+    static __device__ void horizontal(Q<int, N>& r) {
+        lift<1>(r, 12993, -1);
+        lift<0>(r, 434, -1);
+        lift<1>(r, 7233, 1);
+        lift<0>(r, 3633, 1);
+#pragma unroll
+        for (int k = 0; k < N; k += 2) { r.v[k] = fm(r.v[k], 6659); r.v[k + 1] = fm(r.v[k + 1], 5038); }
     }
     static __device__ int single(int x, int) { return x; }                     // dwt.cpp:368
 };
@@ -113,121 +120,239 @@ struct Region {
     int snx, sny;             // number of low-pass columns / rows
 };
 
-// four samples at absolute columns a0..a0+3 of memory row `row` (already reflected) of an
-// interleaved region
-template <typename T>
-__device__ __forceinline__ Q<T> load_quad(const T* __restrict__ base, const Region& g, int row, int a0, bool vec_ok) {
-    Q<T> q;
-    const T* p = base + (size_t)row * g.pitch;
-    if (vec_ok && a0 >= g.x0 && a0 + 3 < g.x1) {
-        int4 t = __ldg(reinterpret_cast<const int4*>(p + (a0 - g.x0)));
-        q.v[0] = *reinterpret_cast<T*>(&t.x); q.v[1] = *reinterpret_cast<T*>(&t.y);
-        q.v[2] = *reinterpret_cast<T*>(&t.z); q.v[3] = *reinterpret_cast<T*>(&t.w);
-    } else {
+// Which 4-column groups of its N columns a lane has to load: owner lanes all of those that come
+// within 4 columns of the region, the halo lane on the left only its last group, the one on the
+// right only its first.
+template <int N>
+__device__ __forceinline__ unsigned group_mask(const Region& g, int a0, int lane, int owners) {
+    unsigned m = 0;
+    if (lane > owners + 1) return 0;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) q.v[k] = __ldg(p + (mirror(a0 + k, g.x0, g.x1) - g.x0));
+    for (int q = 0; q < N / 4; ++q) {
+        const int c = a0 + 4 * q;
+        if (c + 4 > g.x0 - 4 && c < g.x1 + 4) m |= 1u << q;
+    }
+    if (lane == 0) m &= 1u << (N / 4 - 1);
+    if (lane == owners + 1) m &= 1u;
+    return m;
+}
+
+// N samples at absolute columns a0..a0+N-1 of memory row `row` (already reflected) of an
+// interleaved region
+template <typename T, int N>
+__device__ __forceinline__ Q<T, N> load_row(const T* __restrict__ base, const Region& g, int row, int a0, bool vec_ok, unsigned gm) {
+    Q<T, N> q;
+    const T* p = base + (size_t)row * g.pitch;
+#pragma unroll
+    for (int s = 0; s < N / 4; ++s) {
+        const int c = a0 + 4 * s;
+        if (!((gm >> s) & 1u)) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) q.v[4 * s + k] = T(0);
+        } else if (vec_ok && c >= g.x0 && c + 3 < g.x1) {
+            int4 t = __ldg(reinterpret_cast<const int4*>(p + (c - g.x0)));
+            q.v[4 * s + 0] = *reinterpret_cast<T*>(&t.x); q.v[4 * s + 1] = *reinterpret_cast<T*>(&t.y);
+            q.v[4 * s + 2] = *reinterpret_cast<T*>(&t.z); q.v[4 * s + 3] = *reinterpret_cast<T*>(&t.w);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) q.v[4 * s + k] = __ldg(p + (mirror(c + k, g.x0, g.x1) - g.x0));
+        }
     }
     return q;
 }
 
-// store the low pair (columns a0, a0+2) and high pair (a0+1, a0+3) of a finished row into the
+// store the low samples (even columns) and high samples (odd columns) of a finished row into the
 // Mallat row `mrow` of dst
-template <typename T>
-__device__ __forceinline__ void store_split(T* __restrict__ dst, const Region& g, int mrow, int a0, const Q<T>& r) {
+template <typename T, int N>
+__device__ __forceinline__ void store_split(T* __restrict__ dst, const Region& g, int mrow, int a0, const Q<T, N>& r) {
     T* p = dst + (size_t)mrow * g.pitch;
-    int li = (a0 >> 1) - ((g.x0 + 1) >> 1);
-    int hi = (a0 >> 1) - (g.x0 >> 1);
-    T* pl = p + li;
-    T* ph = p + g.snx + hi;
-    bool in0 = a0 >= g.x0 && a0 < g.x1, in1 = a0 + 1 >= g.x0 && a0 + 1 < g.x1;
-    bool in2 = a0 + 2 >= g.x0 && a0 + 2 < g.x1, in3 = a0 + 3 >= g.x0 && a0 + 3 < g.x1;
-    if (in0 && in2 && ((reinterpret_cast<uintptr_t>(pl) & 7) == 0)) {
-        *reinterpret_cast<int2*>(pl) = make_int2(*reinterpret_cast<const int*>(&r.v[0]), *reinterpret_cast<const int*>(&r.v[2]));
-    } else {
-        if (in0) pl[0] = r.v[0];
-        if (in2) pl[1] = r.v[2];
+    T* pl = p + ((a0 >> 1) - ((g.x0 + 1) >> 1));
+    T* ph = p + g.snx + ((a0 >> 1) - (g.x0 >> 1));
+    const bool inside = a0 >= g.x0 && a0 + N - 1 < g.x1;
+    if (N == 8 && inside && (((reinterpret_cast<uintptr_t>(pl) | reinterpret_cast<uintptr_t>(ph)) & 15) == 0)) {
+        *reinterpret_cast<int4*>(pl) = make_int4(*reinterpret_cast<const int*>(&r.v[0]), *reinterpret_cast<const int*>(&r.v[2]),
+                                                 *reinterpret_cast<const int*>(&r.v[N > 4 ? 4 : 0]), *reinterpret_cast<const int*>(&r.v[N > 4 ? 6 : 0]));
+        *reinterpret_cast<int4*>(ph) = make_int4(*reinterpret_cast<const int*>(&r.v[1]), *reinterpret_cast<const int*>(&r.v[3]),
+                                                 *reinterpret_cast<const int*>(&r.v[N > 4 ? 5 : 0]), *reinterpret_cast<const int*>(&r.v[N > 4 ? 7 : 0]));
+        return;
     }
-    if (in1 && in3 && ((reinterpret_cast<uintptr_t>(ph) & 7) == 0)) {
-        *reinterpret_cast<int2*>(ph) = make_int2(*reinterpret_cast<const int*>(&r.v[1]), *reinterpret_cast<const int*>(&r.v[3]));
-    } else {
-        if (in1) ph[0] = r.v[1];
-        if (in3) ph[1] = r.v[3];
+#pragma unroll
+    for (int s = 0; s < N / 4; ++s) {
+        const int c = a0 + 4 * s;
+        T* ql = pl + 2 * s;
+        T* qh = ph + 2 * s;
+        const bool in0 = c >= g.x0 && c < g.x1, in1 = c + 1 >= g.x0 && c + 1 < g.x1;
+        const bool in2 = c + 2 >= g.x0 && c + 2 < g.x1, in3 = c + 3 >= g.x0 && c + 3 < g.x1;
+        if (in0 && in2 && ((reinterpret_cast<uintptr_t>(ql) & 7) == 0)) {
+            *reinterpret_cast<int2*>(ql) = make_int2(*reinterpret_cast<const int*>(&r.v[4 * s]), *reinterpret_cast<const int*>(&r.v[4 * s + 2]));
+        } else {
+            if (in0) ql[0] = r.v[4 * s];
+            if (in2) ql[1] = r.v[4 * s + 2];
+        }
+        if (in1 && in3 && ((reinterpret_cast<uintptr_t>(qh) & 7) == 0)) {
+            *reinterpret_cast<int2*>(qh) = make_int2(*reinterpret_cast<const int*>(&r.v[4 * s + 1]), *reinterpret_cast<const int*>(&r.v[4 * s + 3]));
+        } else {
+            if (in1) qh[0] = r.v[4 * s + 1];
+            if (in3) qh[1] = r.v[4 * s + 3];
+        }
     }
 }
 
-template <class L>
+// Column-interior strips (every column a lane needs lies inside the region and all accesses are
+// naturally aligned) take a branch-free path: predicated 16-byte loads, 8/16-byte stores.
+template <typename T, int N>
+__device__ __forceinline__ Q<T, N> load_row_fast(const T* __restrict__ p, unsigned gm) {
+    Q<T, N> q;
+#pragma unroll
+    for (int s = 0; s < N / 4; ++s) {
+        int4 t = make_int4(0, 0, 0, 0);
+        if ((gm >> s) & 1u) t = __ldg(reinterpret_cast<const int4*>(p + 4 * s));
+        q.v[4 * s + 0] = *reinterpret_cast<T*>(&t.x); q.v[4 * s + 1] = *reinterpret_cast<T*>(&t.y);
+        q.v[4 * s + 2] = *reinterpret_cast<T*>(&t.z); q.v[4 * s + 3] = *reinterpret_cast<T*>(&t.w);
+    }
+    return q;
+}
+template <typename T, int N>
+__device__ __forceinline__ void store_split_fast(T* __restrict__ pl, int snx, const Q<T, N>& r) {
+    T* ph = pl + snx;
+    if (N == 8) {
+        *reinterpret_cast<int4*>(pl) = make_int4(*reinterpret_cast<const int*>(&r.v[0]), *reinterpret_cast<const int*>(&r.v[2]),
+                                                 *reinterpret_cast<const int*>(&r.v[N > 4 ? 4 : 0]), *reinterpret_cast<const int*>(&r.v[N > 4 ? 6 : 0]));
+        *reinterpret_cast<int4*>(ph) = make_int4(*reinterpret_cast<const int*>(&r.v[1]), *reinterpret_cast<const int*>(&r.v[3]),
+                                                 *reinterpret_cast<const int*>(&r.v[N > 4 ? 5 : 0]), *reinterpret_cast<const int*>(&r.v[N > 4 ? 7 : 0]));
+    } else {
+        *reinterpret_cast<int2*>(pl) = make_int2(*reinterpret_cast<const int*>(&r.v[0]), *reinterpret_cast<const int*>(&r.v[2]));
+        *reinterpret_cast<int2*>(ph) = make_int2(*reinterpret_cast<const int*>(&r.v[1]), *reinterpret_cast<const int*>(&r.v[3]));
+    }
+}
+
+struct StripCtx {
+    Region g;
+    int a0, owners, e_first, e_last;
+    unsigned gm;
+    bool owner, vec_ok, wide;
+};
+
+template <class L, int N, int PF, bool FAST>
+__device__ __forceinline__ void forward_rows(const int* __restrict__ src, int* __restrict__ dst, const StripCtx& c) {
+    const Region& g = c.g;
+    const int a0 = c.a0;
+    const int* __restrict__ scol = src + (a0 - g.x0);                       // FAST: this lane's column in row 0
+    int* __restrict__ dcol = dst + ((a0 >> 1) - ((g.x0 + 1) >> 1));         // FAST: low-band position (x0 is even there)
+    auto ld = [&](int n) -> Q<int, N> {
+        const int row = mirror(n, g.y0, g.y1) - g.y0;
+        if (FAST) return load_row_fast<int, N>(scol + (size_t)row * g.pitch, c.gm);
+        return load_row<int, N>(src, g, row, a0, c.vec_ok, c.gm);
+    };
+    L lift;
+    const int n0 = c.e_first + L::LAG - 2 * L::WARM;
+    lift.init(ld(n0 - 2));
+    const int n_end = c.e_last + L::LAG;         // last n of the loop
+    constexpr int D = PF > 0 ? PF : 1;           // row pairs fetched ahead (ring of D pairs)
+    Q<int, N> po[D], pe[D];
+    if (PF) {
+#pragma unroll
+        for (int j = 0; j < D; ++j) if (n0 + 2 * j <= n_end) { po[j] = ld(n0 + 2 * j - 1); pe[j] = ld(n0 + 2 * j); }
+    }
+#pragma unroll 1
+    for (int nb = n0; nb <= n_end; nb += 2 * D * (PF ? 1 : 2)) {
+#pragma unroll
+        for (int j = 0; j < (PF ? D : 2); ++j) {
+            const int n = nb + 2 * j;
+            if (n > n_end) break;
+            Q<int, N> xo, xv;
+            if (PF) {
+                xo = po[j % D]; xv = pe[j % D];
+                if (n + 2 * D <= n_end) { po[j % D] = ld(n + 2 * D - 1); pe[j % D] = ld(n + 2 * D); }
+            } else {
+                xo = ld(n - 1); xv = ld(n);
+            }
+            Q<int, N> lo, hi;
+            lift.step(xo, xv, lo, hi);
+            const int e = n - L::LAG;
+            if (e < c.e_first) continue;                      // warm-up (warp-uniform)
+            if (FAST || c.wide) { L::horizontal(lo); L::horizontal(hi); }
+            else {
+                int oddx = g.x0 & 1;                          // one column: lives at a0 + oddx of the lane owning x0
+                lo.v[oddx] = L::single(lo.v[oddx], oddx); hi.v[oddx] = L::single(hi.v[oddx], oddx);
+            }
+            if (c.owner) {
+                const int mlo = (e >> 1) - ((g.y0 + 1) >> 1), mhi = g.sny + ((e + 1) >> 1) - (g.y0 >> 1);
+                if (FAST) {
+                    if (e >= g.y0 && e < g.y1) store_split_fast<int, N>(dcol + (size_t)mlo * g.pitch, g.snx, lo);
+                    if (e + 1 >= g.y0 && e + 1 < g.y1) store_split_fast<int, N>(dcol + (size_t)mhi * g.pitch, g.snx, hi);
+                } else {
+                    if (e >= g.y0 && e < g.y1) store_split<int, N>(dst, g, mlo, a0, lo);
+                    if (e + 1 >= g.y0 && e + 1 < g.y1) store_split<int, N>(dst, g, mhi, a0, hi);
+                }
+            }
+        }
+    }
+}
+
+template <class L, int N, int PF>
 __global__ void __launch_bounds__(32 * WARPS_PER_CTA)
-k_dwt_forward(const DwtJob* __restrict__ jobs, int seg_pairs) {
+k_dwt_forward(const DwtJob* __restrict__ jobs) {
     const DwtJob job = jobs[blockIdx.y];
     const int lane = threadIdx.x & 31;
     const int item = blockIdx.x * WARPS_PER_CTA + (threadIdx.x >> 5);
     if (item >= job.nstrips * job.nsegs) return;
     const int strip = item % job.nstrips, seg = item / job.nstrips;
-    Region g;
+    const int seg_pairs = job.strip0;
+    StripCtx c;
+    Region& g = c.g;
     g.x0 = job.x0; g.y0 = job.y0; g.x1 = job.x1; g.y1 = job.y1; g.pitch = job.pitch;
     g.snx = ((g.x1 + 1) >> 1) - ((g.x0 + 1) >> 1);
     g.sny = ((g.y1 + 1) >> 1) - ((g.y0 + 1) >> 1);
     const int* __restrict__ src = job.src;
     int* __restrict__ dst = job.dst;
-    const bool vec_ok = ((g.x0 & 1) == 0) && ((g.pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0);
+    c.vec_ok = ((g.x0 & 1) == 0) && ((g.pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0);
     const int xe = g.x0 & ~1, ye = g.y0 & ~1;
-    const int a0 = xe + strip * STRIP_COLS - 4 + lane * 4;       // even absolute column
-    const bool owner = lane >= 1 && lane <= 30;
-    const bool wide = (g.x1 - g.x0) > 1;
-    const int e_first = ye + 2 * seg * seg_pairs;
-    int e_last = e_first + 2 * (seg_pairs - 1);
-    if (e_last > g.y1 - 1) e_last = (g.y1 - 1) & ~1;
+    c.owners = job.strip_cols / N;
+    const int s0 = xe + strip * job.strip_cols;                   // first owned column of the strip
+    c.a0 = s0 - N + lane * N;                                     // even absolute column
+    c.owner = lane >= 1 && lane <= c.owners;
+    c.gm = group_mask<N>(g, c.a0, lane, c.owners);
+    c.wide = (g.x1 - g.x0) > 1;
+    c.e_first = ye + 2 * seg * seg_pairs;
+    c.e_last = c.e_first + 2 * (seg_pairs - 1);
+    if (c.e_last > g.y1 - 1) c.e_last = (g.y1 - 1) & ~1;
 
     if (g.y1 - g.y0 == 1) {                    // single row: no vertical filtering (dwt.cpp:318,323)
         if (seg != 0) return;
-        Q<int> r = load_quad<int>(src, g, 0, a0, vec_ok);
+        Q<int, N> r = load_row<int, N>(src, g, 0, c.a0, c.vec_ok, c.gm);
         int odd = g.y0 & 1;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) r.v[k] = L::single(r.v[k], odd);
-        if (wide) L::horizontal(r);
+        for (int k = 0; k < N; ++k) r.v[k] = L::single(r.v[k], odd);
+        if (c.wide) L::horizontal(r);
         else { int oddx = g.x0 & 1; r.v[oddx] = L::single(r.v[oddx], oddx); }
-        if (owner) store_split<int>(dst, g, 0, a0, r);
+        if (c.owner) store_split<int, N>(dst, g, 0, c.a0, r);
         return;
     }
-
-    L lift;
-    const int n0 = e_first + L::LAG - 2 * L::WARM;
-    lift.init(load_quad<int>(src, g, mirror(n0 - 2, g.y0, g.y1) - g.y0, a0, vec_ok));
-#pragma unroll 2
-    for (int n = n0; n - L::LAG <= e_last; n += 2) {
-        Q<int> xo = load_quad<int>(src, g, mirror(n - 1, g.y0, g.y1) - g.y0, a0, vec_ok);
-        Q<int> xv = load_quad<int>(src, g, mirror(n, g.y0, g.y1) - g.y0, a0, vec_ok);
-        Q<int> lo, hi;
-        lift.step(xo, xv, lo, hi);
-        const int e = n - L::LAG;
-        if (e < e_first) continue;                        // warm-up (warp-uniform)
-        if (wide) { L::horizontal(lo); L::horizontal(hi); }
-        else {
-            int oddx = g.x0 & 1;                          // one column: lives at a0 + oddx of the lane owning x0
-            lo.v[oddx] = L::single(lo.v[oddx], oddx); hi.v[oddx] = L::single(hi.v[oddx], oddx);
-        }
-        if (owner) {
-            if (e >= g.y0 && e < g.y1) store_split<int>(dst, g, (e >> 1) - ((g.y0 + 1) >> 1), a0, lo);
-            if (e + 1 >= g.y0 && e + 1 < g.y1) store_split<int>(dst, g, g.sny + ((e + 1) >> 1) - (g.y0 >> 1), a0, hi);
-        }
-    }
+    // warp-uniform: the strip with its 4-column halos lies inside the region, everything aligned
+    const int align = N == 8 ? 7 : 3;
+    const bool fast = c.vec_ok && s0 - 4 >= g.x0 && s0 + c.owners * N + 4 <= g.x1 && ((s0 - g.x0) & align) == 0 &&
+                      ((g.x0 >> 1) & (align >> 1)) == 0 && (g.snx & (align >> 1)) == 0 &&
+                      ((reinterpret_cast<uintptr_t>(dst) & 15) == 0);
+    if (fast) forward_rows<L, N, PF, true>(src, dst, c);
+    else forward_rows<L, N, PF, false>(src, dst, c);
 }
 
 // ---- lifting kernels (inverse) -----------------------------------------------------------------
 // Vertical streaming step: new low row a = L(n), new high row b = H(n+1); emits the finished pair
 // (row n-LAG, row n-LAG+1).
-struct Inv53 {                 // dwt.cpp:335-352
+template <int N> struct Inv53 {                 // dwt.cpp:335-352
     typedef int T;
     static constexpr int LAG = 2, WARM = 1;
-    Q<int> hprev, sprev;       // H(n-1), s(n-2)
-    __device__ void init(const Q<int>& h) {
+    Q<int, N> hprev, sprev;       // H(n-1), s(n-2)
+    __device__ void init(const Q<int, N>& h) {
         hprev = h;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) sprev.v[k] = 0;
+        for (int k = 0; k < N; ++k) sprev.v[k] = 0;
     }
-    __device__ void step(const Q<int>& a, const Q<int>& b, Q<int>& even, Q<int>& odd) {
+    __device__ void step(const Q<int, N>& a, const Q<int, N>& b, Q<int, N>& even, Q<int, N>& odd) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < N; ++k) {
             int s = a.v[k] - ((hprev.v[k] + b.v[k] + 2) >> 2);
             even.v[k] = sprev.v[k];
             odd.v[k] = hprev.v[k] + ((sprev.v[k] + s) >> 1);
@@ -235,34 +360,34 @@ struct Inv53 {                 // dwt.cpp:335-352
             hprev.v[k] = b.v[k];
         }
     }
-    static __device__ void horizontal(Q<int>& r) {
+    static __device__ void horizontal(Q<int, N>& r) {
         const unsigned m = 0xffffffffu;
-        int pv = __shfl_up_sync(m, r.v[3], 1);
-        r.v[0] -= (pv + r.v[1] + 2) >> 2;
-        r.v[2] -= (r.v[1] + r.v[3] + 2) >> 2;
-        int nx = __shfl_down_sync(m, r.v[0], 1);
-        r.v[1] += (r.v[0] + r.v[2]) >> 1;
-        r.v[3] += (r.v[2] + nx) >> 1;
+        const int pv = __shfl_up_sync(m, r.v[N - 1], 1);
+#pragma unroll
+        for (int k = 0; k < N; k += 2) r.v[k] -= ((k ? r.v[k ? k - 1 : 0] : pv) + r.v[k + 1] + 2) >> 2;
+        const int nx = __shfl_down_sync(m, r.v[0], 1);
+#pragma unroll
+        for (int k = 1; k < N; k += 2) r.v[k] += (r.v[k - 1] + (k + 1 < N ? r.v[k + 1 < N ? k + 1 : 0] : nx)) >> 1;
     }
     static __device__ int single(int x, int odd) { return odd ? x / 2 : x; }   // dwt.cpp:340,345
 };
 
-struct Inv97 {                 // float, dwt.cpp:769-921; constants :94-100
+template <int N> struct Inv97 {                 // float, dwt.cpp:769-921; constants :94-100
     typedef float T;
     static constexpr int LAG = 4, WARM = 3;
     static constexpr float K = 1.230174105f, C = 1.625732422f;
     static constexpr float ALPHA = 1.586134342f, BETA = 0.052980118f, GAMMA = -0.882911075f, DELTA = -0.443506852f;
-    Q<float> b1, e1, o1, e2;   // b(n-1), e1(n-2), o1(n-3), e2(n-4)
+    Q<float, N> b1, e1, o1, e2;   // b(n-1), e1(n-2), o1(n-3), e2(n-4)
     static __device__ __forceinline__ float lift(float x, float l, float r, float c) {
         return __fadd_rn(x, __fmul_rn(__fadd_rn(l, r), c));     // no FMA contraction
     }
-    __device__ void init(const Q<float>& h) {
+    __device__ void init(const Q<float, N>& h) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) { b1.v[k] = __fmul_rn(h.v[k], C); e1.v[k] = o1.v[k] = e2.v[k] = 0.f; }
+        for (int k = 0; k < N; ++k) { b1.v[k] = __fmul_rn(h.v[k], C); e1.v[k] = o1.v[k] = e2.v[k] = 0.f; }
     }
-    __device__ void step(const Q<float>& a, const Q<float>& b, Q<float>& even, Q<float>& odd) {
+    __device__ void step(const Q<float, N>& a, const Q<float, N>& b, Q<float, N>& even, Q<float, N>& odd) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < N; ++k) {
             float an = __fmul_rn(a.v[k], K), bn = __fmul_rn(b.v[k], C);
             float ne1 = lift(an, b1.v[k], bn, DELTA);
             float no1 = lift(b1.v[k], e1.v[k], ne1, GAMMA);
@@ -273,62 +398,88 @@ struct Inv97 {                 // float, dwt.cpp:769-921; constants :94-100
             b1.v[k] = bn; e1.v[k] = ne1; o1.v[k] = no1; e2.v[k] = ne2;
         }
     }
-    static __device__ void horizontal(Q<float>& r) {
+    template <int ODD> static __device__ __forceinline__ void hlift(Q<float, N>& r, float c) {
         const unsigned m = 0xffffffffu;
-        r.v[0] = __fmul_rn(r.v[0], K); r.v[2] = __fmul_rn(r.v[2], K);
-        r.v[1] = __fmul_rn(r.v[1], C); r.v[3] = __fmul_rn(r.v[3], C);
-        float pv = __shfl_up_sync(m, r.v[3], 1);
-        r.v[0] = lift(r.v[0], pv, r.v[1], DELTA);
-        r.v[2] = lift(r.v[2], r.v[1], r.v[3], DELTA);
-        float nx = __shfl_down_sync(m, r.v[0], 1);
-        r.v[1] = lift(r.v[1], r.v[0], r.v[2], GAMMA);
-        r.v[3] = lift(r.v[3], r.v[2], nx, GAMMA);
-        pv = __shfl_up_sync(m, r.v[3], 1);
-        r.v[0] = lift(r.v[0], pv, r.v[1], BETA);
-        r.v[2] = lift(r.v[2], r.v[1], r.v[3], BETA);
-        nx = __shfl_down_sync(m, r.v[0], 1);
-        r.v[1] = lift(r.v[1], r.v[0], r.v[2], ALPHA);
-        r.v[3] = lift(r.v[3], r.v[2], nx, ALPHA);
+        if (ODD) {
+            const float nx = __shfl_down_sync(m, r.v[0], 1);
+#pragma unroll
+            for (int k = 1; k < N; k += 2) r.v[k] = lift(r.v[k], r.v[k - 1], (k + 1 < N ? r.v[k + 1 < N ? k + 1 : 0] : nx), c);
+        } else {
+            const float pv = __shfl_up_sync(m, r.v[N - 1], 1);
+#pragma unroll
+            for (int k = 0; k < N; k += 2) r.v[k] = lift(r.v[k], (k ? r.v[k ? k - 1 : 0] : pv), r.v[k + 1], c);
+        }
+    }
+    static __device__ void horizontal(Q<float, N>& r) {
+#pragma unroll
+        for (int k = 0; k < N; k += 2) { r.v[k] = __fmul_rn(r.v[k], K); r.v[k + 1] = __fmul_rn(r.v[k + 1], C); }
+        hlift<0>(r, DELTA);
+        hlift<1>(r, GAMMA);
+        hlift<0>(r, BETA);
+        hlift<1>(r, ALPHA);
     }
     static __device__ float single(float x, int) { return x; }
 };
 
-// four interleaved samples at absolute columns a0..a0+3 gathered from the low and high halves of
+// N interleaved samples at absolute columns a0..a0+N-1 gathered from the low and high halves of
 // Mallat row `mrow`
-template <typename T>
-__device__ __forceinline__ Q<T> load_split(const T* __restrict__ base, const Region& g, int mrow, int a0) {
-    Q<T> q;
+template <typename T, int N>
+__device__ __forceinline__ Q<T, N> load_split(const T* __restrict__ base, const Region& g, int mrow, int a0, unsigned gm) {
+    Q<T, N> q;
     const T* p = base + (size_t)mrow * g.pitch;
     const int cl = (g.x0 + 1) >> 1, ch = g.x0 >> 1;
-    if (a0 >= g.x0 && a0 + 3 < g.x1) {
+    if (N == 8 && gm == 3u && a0 >= g.x0 && a0 + N - 1 < g.x1) {
         const T* pl = p + ((a0 >> 1) - cl);
         const T* ph = p + g.snx + ((a0 >> 1) - ch);
-        if (((reinterpret_cast<uintptr_t>(pl) | reinterpret_cast<uintptr_t>(ph)) & 7) == 0) {
-            int2 l = __ldg(reinterpret_cast<const int2*>(pl)), h = __ldg(reinterpret_cast<const int2*>(ph));
+        if (((reinterpret_cast<uintptr_t>(pl) | reinterpret_cast<uintptr_t>(ph)) & 15) == 0) {
+            int4 l = __ldg(reinterpret_cast<const int4*>(pl)), h = __ldg(reinterpret_cast<const int4*>(ph));
             q.v[0] = *reinterpret_cast<T*>(&l.x); q.v[2] = *reinterpret_cast<T*>(&l.y);
+            q.v[N > 4 ? 4 : 0] = *reinterpret_cast<T*>(&l.z); q.v[N > 4 ? 6 : 0] = *reinterpret_cast<T*>(&l.w);
             q.v[1] = *reinterpret_cast<T*>(&h.x); q.v[3] = *reinterpret_cast<T*>(&h.y);
-        } else {
-            q.v[0] = __ldg(pl); q.v[2] = __ldg(pl + 1); q.v[1] = __ldg(ph); q.v[3] = __ldg(ph + 1);
+            q.v[N > 4 ? 5 : 0] = *reinterpret_cast<T*>(&h.z); q.v[N > 4 ? 7 : 0] = *reinterpret_cast<T*>(&h.w);
+            return q;
         }
-    } else {
+    }
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            int a = mirror(a0 + k, g.x0, g.x1);
-            q.v[k] = (a & 1) ? __ldg(p + g.snx + ((a >> 1) - ch)) : __ldg(p + ((a >> 1) - cl));
+    for (int s = 0; s < N / 4; ++s) {
+        const int c = a0 + 4 * s;
+        if (!((gm >> s) & 1u)) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) q.v[4 * s + k] = T(0);
+        } else if (c >= g.x0 && c + 3 < g.x1) {
+            const T* pl = p + ((c >> 1) - cl);
+            const T* ph = p + g.snx + ((c >> 1) - ch);
+            if (((reinterpret_cast<uintptr_t>(pl) | reinterpret_cast<uintptr_t>(ph)) & 7) == 0) {
+                int2 l = __ldg(reinterpret_cast<const int2*>(pl)), h = __ldg(reinterpret_cast<const int2*>(ph));
+                q.v[4 * s + 0] = *reinterpret_cast<T*>(&l.x); q.v[4 * s + 2] = *reinterpret_cast<T*>(&l.y);
+                q.v[4 * s + 1] = *reinterpret_cast<T*>(&h.x); q.v[4 * s + 3] = *reinterpret_cast<T*>(&h.y);
+            } else {
+                q.v[4 * s + 0] = __ldg(pl); q.v[4 * s + 2] = __ldg(pl + 1); q.v[4 * s + 1] = __ldg(ph); q.v[4 * s + 3] = __ldg(ph + 1);
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                int a = mirror(c + k, g.x0, g.x1);
+                q.v[4 * s + k] = (a & 1) ? __ldg(p + g.snx + ((a >> 1) - ch)) : __ldg(p + ((a >> 1) - cl));
+            }
         }
     }
     return q;
 }
 
-template <typename T>
-__device__ __forceinline__ void store_quad(T* __restrict__ dst, const Region& g, int row, int a0, const Q<T>& r, bool vec_ok) {
+template <typename T, int N>
+__device__ __forceinline__ void store_row(T* __restrict__ dst, const Region& g, int row, int a0, const Q<T, N>& r, bool vec_ok) {
     T* p = dst + (size_t)row * g.pitch + (a0 - g.x0);
-    if (vec_ok && a0 >= g.x0 && a0 + 3 < g.x1) {
-        *reinterpret_cast<int4*>(p) = make_int4(*reinterpret_cast<const int*>(&r.v[0]), *reinterpret_cast<const int*>(&r.v[1]),
-                                                *reinterpret_cast<const int*>(&r.v[2]), *reinterpret_cast<const int*>(&r.v[3]));
-    } else {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) if (a0 + k >= g.x0 && a0 + k < g.x1) p[k] = r.v[k];
+    for (int s = 0; s < N / 4; ++s) {
+        const int c = a0 + 4 * s;
+        if (vec_ok && c >= g.x0 && c + 3 < g.x1) {
+            *reinterpret_cast<int4*>(p + 4 * s) = make_int4(*reinterpret_cast<const int*>(&r.v[4 * s]), *reinterpret_cast<const int*>(&r.v[4 * s + 1]),
+                                                            *reinterpret_cast<const int*>(&r.v[4 * s + 2]), *reinterpret_cast<const int*>(&r.v[4 * s + 3]));
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) if (c + k >= g.x0 && c + k < g.x1) p[4 * s + k] = r.v[4 * s + k];
+        }
     }
 }
 
@@ -338,90 +489,219 @@ __device__ __forceinline__ int mallat_row(const Region& g, int n) {
     return (r & 1) ? g.sny + ((r >> 1) - (g.y0 >> 1)) : (r >> 1) - ((g.y0 + 1) >> 1);
 }
 
-template <class L>
+template <typename T, int N>
+__device__ __forceinline__ Q<T, N> load_split_fast(const T* __restrict__ pl, int snx, unsigned gm) {
+    Q<T, N> q;
+    const T* ph = pl + snx;
+    if (N == 8) {
+        // owner lanes take both groups with 16-byte loads, halo lanes one group with 8-byte loads
+        int4 l = make_int4(0, 0, 0, 0), h = make_int4(0, 0, 0, 0);
+        if (gm == 3u) { l = __ldg(reinterpret_cast<const int4*>(pl)); h = __ldg(reinterpret_cast<const int4*>(ph)); }
+        else if (gm == 1u) {
+            int2 a = __ldg(reinterpret_cast<const int2*>(pl)), b = __ldg(reinterpret_cast<const int2*>(ph));
+            l.x = a.x; l.y = a.y; h.x = b.x; h.y = b.y;
+        } else if (gm == 2u) {
+            int2 a = __ldg(reinterpret_cast<const int2*>(pl + 2)), b = __ldg(reinterpret_cast<const int2*>(ph + 2));
+            l.z = a.x; l.w = a.y; h.z = b.x; h.w = b.y;
+        }
+        q.v[0] = *reinterpret_cast<T*>(&l.x); q.v[2] = *reinterpret_cast<T*>(&l.y);
+        q.v[N > 4 ? 4 : 0] = *reinterpret_cast<T*>(&l.z); q.v[N > 4 ? 6 : 0] = *reinterpret_cast<T*>(&l.w);
+        q.v[1] = *reinterpret_cast<T*>(&h.x); q.v[3] = *reinterpret_cast<T*>(&h.y);
+        q.v[N > 4 ? 5 : 0] = *reinterpret_cast<T*>(&h.z); q.v[N > 4 ? 7 : 0] = *reinterpret_cast<T*>(&h.w);
+    } else {
+        int2 l = make_int2(0, 0), h = make_int2(0, 0);
+        if (gm & 1u) { l = __ldg(reinterpret_cast<const int2*>(pl)); h = __ldg(reinterpret_cast<const int2*>(ph)); }
+        q.v[0] = *reinterpret_cast<T*>(&l.x); q.v[2] = *reinterpret_cast<T*>(&l.y);
+        q.v[1] = *reinterpret_cast<T*>(&h.x); q.v[3] = *reinterpret_cast<T*>(&h.y);
+    }
+    return q;
+}
+template <typename T, int N>
+__device__ __forceinline__ void store_row_fast(T* __restrict__ p, const Q<T, N>& r) {
+#pragma unroll
+    for (int s = 0; s < N / 4; ++s)
+        *reinterpret_cast<int4*>(p + 4 * s) = make_int4(*reinterpret_cast<const int*>(&r.v[4 * s]), *reinterpret_cast<const int*>(&r.v[4 * s + 1]),
+                                                        *reinterpret_cast<const int*>(&r.v[4 * s + 2]), *reinterpret_cast<const int*>(&r.v[4 * s + 3]));
+}
+
+template <class L, int N, int PF, bool FAST>
+__device__ __forceinline__ void inverse_rows(const typename L::T* __restrict__ src, typename L::T* __restrict__ dst, const StripCtx& c) {
+    typedef typename L::T T;
+    const Region& g = c.g;
+    const int a0 = c.a0;
+    const int oddx = g.x0 & 1;
+    const T* __restrict__ scol = src + ((a0 >> 1) - ((g.x0 + 1) >> 1));     // FAST: low-band position
+    T* __restrict__ dcol = dst + (a0 - g.x0);
+    auto ld = [&](int n) -> Q<T, N> {
+        const int mrow = mallat_row(g, n);
+        Q<T, N> q = FAST ? load_split_fast<T, N>(scol + (size_t)mrow * g.pitch, g.snx, c.gm)
+                         : load_split<T, N>(src, g, mrow, a0, c.gm);
+        return q;
+    };
+    auto hz = [&](Q<T, N>& q) {
+        if (FAST || c.wide) L::horizontal(q); else q.v[oddx] = L::single(q.v[oddx], oddx);
+    };
+    L lift;
+    const int n0 = c.e_first + L::LAG - 2 * L::WARM;
+    {
+        Q<T, N> h = ld(n0 - 1);
+        hz(h);
+        lift.init(h);
+    }
+    const int n_end = c.e_last + L::LAG;
+    constexpr int D = PF > 0 ? PF : 1;
+    Q<T, N> pa[D], pb[D];
+    if (PF) {
+#pragma unroll
+        for (int j = 0; j < D; ++j) if (n0 + 2 * j <= n_end) { pa[j] = ld(n0 + 2 * j); pb[j] = ld(n0 + 2 * j + 1); }
+    }
+#pragma unroll 1
+    for (int nb = n0; nb <= n_end; nb += 2 * D * (PF ? 1 : 2)) {
+#pragma unroll
+        for (int j = 0; j < (PF ? D : 2); ++j) {
+            const int n = nb + 2 * j;
+            if (n > n_end) break;
+            Q<T, N> a, b;
+            if (PF) {
+                a = pa[j % D]; b = pb[j % D];
+                if (n + 2 * D <= n_end) { pa[j % D] = ld(n + 2 * D); pb[j % D] = ld(n + 2 * D + 1); }
+            } else {
+                a = ld(n); b = ld(n + 1);
+            }
+            hz(a); hz(b);
+            Q<T, N> ev, od;
+            lift.step(a, b, ev, od);
+            const int e = n - L::LAG;
+            if (e < c.e_first || !c.owner) continue;
+            if (FAST) {
+                if (e >= g.y0 && e < g.y1) store_row_fast<T, N>(dcol + (size_t)(e - g.y0) * g.pitch, ev);
+                if (e + 1 >= g.y0 && e + 1 < g.y1) store_row_fast<T, N>(dcol + (size_t)(e + 1 - g.y0) * g.pitch, od);
+            } else {
+                if (e >= g.y0 && e < g.y1) store_row<T, N>(dst, g, e - g.y0, a0, ev, c.vec_ok);
+                if (e + 1 >= g.y0 && e + 1 < g.y1) store_row<T, N>(dst, g, e + 1 - g.y0, a0, od, c.vec_ok);
+            }
+        }
+    }
+}
+
+template <class L, int N, int PF>
 __global__ void __launch_bounds__(32 * WARPS_PER_CTA)
-k_dwt_inverse(const DwtJob* __restrict__ jobs, int seg_pairs) {
+k_dwt_inverse(const DwtJob* __restrict__ jobs) {
     typedef typename L::T T;
     const DwtJob job = jobs[blockIdx.y];
     const int lane = threadIdx.x & 31;
     const int item = blockIdx.x * WARPS_PER_CTA + (threadIdx.x >> 5);
     if (item >= job.nstrips * job.nsegs) return;
     const int strip = item % job.nstrips, seg = item / job.nstrips;
-    Region g;
+    const int seg_pairs = job.strip0;
+    StripCtx c;
+    Region& g = c.g;
     g.x0 = job.x0; g.y0 = job.y0; g.x1 = job.x1; g.y1 = job.y1; g.pitch = job.pitch;
     g.snx = ((g.x1 + 1) >> 1) - ((g.x0 + 1) >> 1);
     g.sny = ((g.y1 + 1) >> 1) - ((g.y0 + 1) >> 1);
     const T* __restrict__ src = reinterpret_cast<const T*>(job.src);
     T* __restrict__ dst = reinterpret_cast<T*>(job.dst);
-    const bool vec_ok = ((g.x0 & 1) == 0) && ((g.pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0);
+    c.vec_ok = ((g.x0 & 1) == 0) && ((g.pitch & 3) == 0) && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0);
     const int xe = g.x0 & ~1, ye = g.y0 & ~1;
-    const int a0 = xe + strip * STRIP_COLS - 4 + lane * 4;
-    const bool owner = lane >= 1 && lane <= 30;
-    const bool wide = (g.x1 - g.x0) > 1;
+    c.owners = job.strip_cols / N;
+    const int s0 = xe + strip * job.strip_cols;
+    c.a0 = s0 - N + lane * N;
+    c.owner = lane >= 1 && lane <= c.owners;
+    c.gm = group_mask<N>(g, c.a0, lane, c.owners);
+    c.wide = (g.x1 - g.x0) > 1;
     const int oddx = g.x0 & 1;
-    const int e_first = ye + 2 * seg * seg_pairs;
-    int e_last = e_first + 2 * (seg_pairs - 1);
-    if (e_last > g.y1 - 1) e_last = (g.y1 - 1) & ~1;
+    c.e_first = ye + 2 * seg * seg_pairs;
+    c.e_last = c.e_first + 2 * (seg_pairs - 1);
+    if (c.e_last > g.y1 - 1) c.e_last = (g.y1 - 1) & ~1;
 
     if (g.y1 - g.y0 == 1) {
         if (seg != 0) return;
-        Q<T> r = load_split<T>(src, g, 0, a0);
-        if (wide) L::horizontal(r); else r.v[oddx] = L::single(r.v[oddx], oddx);
+        Q<T, N> r = load_split<T, N>(src, g, 0, c.a0, c.gm);
+        if (c.wide) L::horizontal(r); else r.v[oddx] = L::single(r.v[oddx], oddx);
         int odd = g.y0 & 1;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) r.v[k] = L::single(r.v[k], odd);
-        if (owner) store_quad<T>(dst, g, 0, a0, r, vec_ok);
+        for (int k = 0; k < N; ++k) r.v[k] = L::single(r.v[k], odd);
+        if (c.owner) store_row<T, N>(dst, g, 0, c.a0, r, c.vec_ok);
         return;
     }
-
-    L lift;
-    const int n0 = e_first + L::LAG - 2 * L::WARM;
-    {
-        Q<T> h = load_split<T>(src, g, mallat_row(g, n0 - 1), a0);
-        if (wide) L::horizontal(h); else h.v[oddx] = L::single(h.v[oddx], oddx);
-        lift.init(h);
-    }
-#pragma unroll 2
-    for (int n = n0; n - L::LAG <= e_last; n += 2) {
-        Q<T> a = load_split<T>(src, g, mallat_row(g, n), a0);
-        Q<T> b = load_split<T>(src, g, mallat_row(g, n + 1), a0);
-        if (wide) { L::horizontal(a); L::horizontal(b); }
-        else { a.v[oddx] = L::single(a.v[oddx], oddx); b.v[oddx] = L::single(b.v[oddx], oddx); }
-        Q<T> ev, od;
-        lift.step(a, b, ev, od);
-        const int e = n - L::LAG;
-        if (e < e_first || !owner) continue;
-        if (e >= g.y0 && e < g.y1) store_quad<T>(dst, g, e - g.y0, a0, ev, vec_ok);
-        if (e + 1 >= g.y0 && e + 1 < g.y1) store_quad<T>(dst, g, e + 1 - g.y0, a0, od, vec_ok);
-    }
+    const int align = N == 8 ? 7 : 3;
+    const bool fast = c.vec_ok && s0 - 4 >= g.x0 && s0 + c.owners * N + 4 <= g.x1 && ((s0 - g.x0) & align) == 0 &&
+                      ((g.x0 >> 1) & (align >> 1)) == 0 && (g.snx & (align >> 1)) == 0 &&
+                      ((reinterpret_cast<uintptr_t>(src) & 15) == 0);
+    if (fast) inverse_rows<L, N, PF, true>(src, dst, c);
+    else inverse_rows<L, N, PF, false>(src, dst, c);
 }
 
 }  // namespace
 
+// Tunables (overridable through the environment for sweeps): columns per lane, software prefetch,
+// and the number of warp work items a launch should at least offer the 148 SMs.
+struct DwtTune { int ncol, pf_fwd, pf_inv, min_items, owners, gran; };
+static const DwtTune& tune() {
+    static DwtTune t = [] {
+        DwtTune v{4, 1, 2, 148 * 96, 30, 1};
+        auto geti = [](const char* name, int dflt) { const char* s = getenv(name); return s ? atoi(s) : dflt; };
+        v.ncol = geti("J2KCUDA_DWT_NCOL", v.ncol) == 8 ? 8 : 4;
+        v.pf_fwd = geti("J2KCUDA_DWT_PF", v.pf_fwd);
+        v.pf_inv = geti("J2KCUDA_DWT_PF_INV", getenv("J2KCUDA_DWT_PF") ? v.pf_fwd : v.pf_inv);
+        if (v.pf_fwd < 0) v.pf_fwd = 0; if (v.pf_fwd > 3) v.pf_fwd = 3;
+        if (v.pf_inv < 0) v.pf_inv = 0; if (v.pf_inv > 3) v.pf_inv = 3;
+        v.min_items = geti("J2KCUDA_DWT_ITEMS", v.min_items);
+        if (v.min_items < 1) v.min_items = 1;
+        v.owners = geti("J2KCUDA_DWT_OWNERS", v.owners);
+        if (v.owners < 1 || v.owners > 30) v.owners = 30;
+        v.gran = geti("J2KCUDA_DWT_GRAN", v.gran);
+        if (v.gran < 1 || v.gran > v.owners) v.gran = 1;
+        return v;
+    }();
+    return t;
+}
+
+// Strips are balanced: the row is cut into chunks of `ncol` columns, at most `owners` chunks (owner
+// lanes, <= 30) per warp, and every strip of a job gets the same number of chunks (a multiple of
+// `gran`, which keeps strip starts on sector / line boundaries).
+static void strip_geometry(const DwtJob& j, int ncol, int& nstrips, int& strip_cols) {
+    const DwtTune& t = tune();
+    const int xe = j.x0 & ~1;
+    const int chunks = (j.x1 - xe + ncol - 1) / ncol;
+    nstrips = (chunks + t.owners - 1) / t.owners;
+    if (nstrips < 1) nstrips = 1;
+    int per = (chunks + nstrips - 1) / nstrips;
+    per = (per + t.gran - 1) / t.gran * t.gran;
+    if (per > 30) per = 30;
+    if (per < 1) per = 1;
+    nstrips = (chunks + per - 1) / per;
+    if (nstrips < 1) nstrips = 1;
+    strip_cols = per * ncol;
+}
+
 // Segment length: long enough that the warm-up rows are a few percent, short enough that one
 // level of one 4K frame still gives every SM a dozen or more warps.
 static int pick_seg_pairs(const DwtJob* jobs, int njobs) {
+    const DwtTune& t = tune();
     long long best = 64;
-    for (int sp = 64; sp >= 8; sp >>= 1) {
+    for (int sp = 64; sp >= 2; sp >>= 1) {
         long long items = 0;
         for (int i = 0; i < njobs; ++i) {
-            int xe = jobs[i].x0 & ~1, ye = jobs[i].y0 & ~1;
-            long long strips = (jobs[i].x1 - xe + STRIP_COLS - 1) / STRIP_COLS;
+            int ns, sc;
+            strip_geometry(jobs[i], t.ncol, ns, sc);
+            const int ye = jobs[i].y0 & ~1;
             long long pairs = (((jobs[i].y1 + 1) & ~1) - ye) / 2;
-            items += strips * ((pairs + sp - 1) / sp);
+            items += (long long)ns * ((pairs + sp - 1) / sp);
         }
         best = sp;
-        if (items >= 148LL * 24) break;
+        if (items >= t.min_items) break;
     }
     return (int)best;
 }
 
 int dwt_plan_jobs(DwtJob* jobs, int njobs) {
+    const DwtTune& t = tune();
     int sp = pick_seg_pairs(jobs, njobs);
     int max_items = 0;
     for (int i = 0; i < njobs; ++i) {
-        int xe = jobs[i].x0 & ~1, ye = jobs[i].y0 & ~1;
-        jobs[i].nstrips = (jobs[i].x1 - xe + STRIP_COLS - 1) / STRIP_COLS;
+        const int ye = jobs[i].y0 & ~1;
+        strip_geometry(jobs[i], t.ncol, jobs[i].nstrips, jobs[i].strip_cols);
         int pairs = (((jobs[i].y1 + 1) & ~1) - ye) / 2;
         jobs[i].nsegs = (pairs + sp - 1) / sp;
         jobs[i].strip0 = sp;
@@ -431,18 +711,47 @@ int dwt_plan_jobs(DwtJob* jobs, int njobs) {
     return max_items;
 }
 
-void launch_dwt_forward(const DwtJob* d_jobs, int njobs, int max_items, int seg_pairs, int kind, cudaStream_t st) {
-    if (njobs <= 0 || max_items <= 0) return;
-    dim3 grid((max_items + WARPS_PER_CTA - 1) / WARPS_PER_CTA, njobs), block(32 * WARPS_PER_CTA);
-    if (kind == DWT_53) k_dwt_forward<Fwd53><<<grid, block, 0, st>>>(d_jobs, seg_pairs);
-    else k_dwt_forward<Fwd97><<<grid, block, 0, st>>>(d_jobs, seg_pairs);
+template <template <int> class L, int N>
+static void launch_fwd_n(dim3 grid, dim3 block, cudaStream_t st, const DwtJob* d_jobs, int pf) {
+    switch (pf) {
+    case 0: k_dwt_forward<L<N>, N, 0><<<grid, block, 0, st>>>(d_jobs); break;
+    case 1: k_dwt_forward<L<N>, N, 1><<<grid, block, 0, st>>>(d_jobs); break;
+    case 2: k_dwt_forward<L<N>, N, 2><<<grid, block, 0, st>>>(d_jobs); break;
+    default: k_dwt_forward<L<N>, N, 3><<<grid, block, 0, st>>>(d_jobs); break;
+    }
+}
+template <template <int> class L, int N>
+static void launch_inv_n(dim3 grid, dim3 block, cudaStream_t st, const DwtJob* d_jobs, int pf) {
+    switch (pf) {
+    case 0: k_dwt_inverse<L<N>, N, 0><<<grid, block, 0, st>>>(d_jobs); break;
+    case 1: k_dwt_inverse<L<N>, N, 1><<<grid, block, 0, st>>>(d_jobs); break;
+    case 2: k_dwt_inverse<L<N>, N, 2><<<grid, block, 0, st>>>(d_jobs); break;
+    default: k_dwt_inverse<L<N>, N, 3><<<grid, block, 0, st>>>(d_jobs); break;
+    }
+}
+template <template <int> class L>
+static void launch_fwd(dim3 grid, dim3 block, cudaStream_t st, const DwtJob* d_jobs) {
+    const DwtTune& t = tune();
+    if (t.ncol == 8) launch_fwd_n<L, 8>(grid, block, st, d_jobs, t.pf_fwd); else launch_fwd_n<L, 4>(grid, block, st, d_jobs, t.pf_fwd);
+}
+template <template <int> class L>
+static void launch_inv(dim3 grid, dim3 block, cudaStream_t st, const DwtJob* d_jobs) {
+    const DwtTune& t = tune();
+    if (t.ncol == 8) launch_inv_n<L, 8>(grid, block, st, d_jobs, t.pf_inv); else launch_inv_n<L, 4>(grid, block, st, d_jobs, t.pf_inv);
 }
 
-void launch_dwt_inverse(const DwtJob* d_jobs, int njobs, int max_items, int seg_pairs, int kind, cudaStream_t st) {
+void launch_dwt_forward(const DwtJob* d_jobs, int njobs, int max_items, int /*seg_pairs*/, int kind, cudaStream_t st) {
     if (njobs <= 0 || max_items <= 0) return;
     dim3 grid((max_items + WARPS_PER_CTA - 1) / WARPS_PER_CTA, njobs), block(32 * WARPS_PER_CTA);
-    if (kind == DWT_53) k_dwt_inverse<Inv53><<<grid, block, 0, st>>>(d_jobs, seg_pairs);
-    else k_dwt_inverse<Inv97><<<grid, block, 0, st>>>(d_jobs, seg_pairs);
+    if (kind == DWT_53) launch_fwd<Fwd53>(grid, block, st, d_jobs);
+    else launch_fwd<Fwd97>(grid, block, st, d_jobs);
+}
+
+void launch_dwt_inverse(const DwtJob* d_jobs, int njobs, int max_items, int /*seg_pairs*/, int kind, cudaStream_t st) {
+    if (njobs <= 0 || max_items <= 0) return;
+    dim3 grid((max_items + WARPS_PER_CTA - 1) / WARPS_PER_CTA, njobs), block(32 * WARPS_PER_CTA);
+    if (kind == DWT_53) launch_inv<Inv53>(grid, block, st, d_jobs);
+    else launch_inv<Inv97>(grid, block, st, d_jobs);
 }
 
 }  // namespace j2k

@@ -70,7 +70,9 @@ def run_decode(h, w, nc, prec, kind, reps=5, **kw):
 
 
 if __name__ == "__main__":
-    if "decode" in sys.argv:
+    if "dwt" in sys.argv:
+        run(2160, 4096, 4, 16, "smooth", reps=6, mct=1)
+    elif "decode" in sys.argv:
         for kind in ("smooth", "noise"):
             run_decode(2160, 4096, 4, 16, kind, mct=1)
         run_decode(1080, 2048, 3, 8, "smooth", mct=1)
