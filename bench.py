@@ -1,8 +1,10 @@
 #!/usr/bin/env python
 """bench.py -- 4K lossless JPEG 2000 throughput of libj2kcuda on B200 (BASELINE.json metric).
 
-A step = one pass of the hot path over one 4096x2160 16-bit RGBA frame (BASELINE configs[1]):
-lossless 5/3, RCT on components 0-2, 6 resolutions, 64x64 code-blocks, LRCP, one layer, single tile.
+A step = one pass of the hot path (encode, then decode what was encoded) over one batch of FRAMES
+4096x2160 16-bit RGBA frames (BASELINE configs[1]): lossless 5/3, RCT on components 0-2, 6 resolutions,
+64x64 code-blocks, LRCP, one layer, single tile.  Frames go through j2kcuda_sequence_encode / _decode,
+which keep several frames in flight (independent frames, no exchange).
   value  MPix/s with the frame already resident in HBM (device stages + result D2H + host Tier-2)
   e2e    MPix/s through the reference-facing C-ABI calls with pinned HOST buffers (H2D and D2H inside)
   roofline  the DWT level-1 kernel: algorithmic bytes (8 B per sample per component) / its CUDA-event time
@@ -27,7 +29,10 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 W, H, NC, PREC = 4096, 2160, 4, 16
 WORKLOAD = "4096x2160 16-bit RGBA lossless 5/3 (RCT, 6 resolutions, 64x64 code-blocks, 1 tile)"
-NROT = 4   # distinct frames rotated through: 4 x 70.8 MB input + 283 MB of planes per frame > 126 MB L2
+FRAMES = 8   # frames per step per GPU (one batch of the image sequence): 8 x 70.8 MB of input and 283 MB of
+             # planes per frame in flight -- far beyond the 126 MB L2, so no flush is needed between steps
+TRAFFIC_L1 = None   # dram bytes per level-1 launch from the ncu --set full capture (profiles/), filled in when captured
+WORKERS = 4  # contexts (stream + buffers + host thread) the sequence keeps in flight
 
 
 def peaks():
@@ -105,7 +110,7 @@ def run_reference(args, rank):
         "impl": "reference", "metric": "4K lossless encode+decode MPix/s", "value": v, "unit": "MPix/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic (%s)" % args.kind,
-        "config": {"workload": WORKLOAD, "direction": "encode then decode of the same frame"},
+        "config": {"workload": WORKLOAD, "direction": "encode then decode of the same frame", "frames_per_step_per_gpu": 1},
         "cpu_baseline": {"value": v, "unit": "MPix/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "MPix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
@@ -113,10 +118,12 @@ def run_reference(args, rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=6)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--kind", default="smooth", choices=["smooth", "noise", "ramp"])
+    ap.add_argument("--frames", type=int, default=FRAMES)
+    ap.add_argument("--workers", type=int, default=WORKERS)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -129,7 +136,7 @@ def main():
     import torch
     import torch.distributed as dist
     from j2k_b200 import _lib as L
-    from j2k_b200.frames import make_frame
+    from j2k_b200.frames import make_frame, shard_frames
     import j2k
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: libj2kcuda has no CPU path")
@@ -137,137 +144,167 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     lib = L.lib()
-    lib.j2kcuda_encoder_create.restype = C.c_void_p
+    F = args.frames
     p = L.default_params(width=W, height=H, ncomp=NC, prec=PREC, mct=1, numresolution=6, device=local)
-    enc = C.c_void_p(lib.j2kcuda_encoder_create(C.byref(p)))
-    if not enc.value:
-        raise SystemExit("encoder_create failed: " + L.last_error())
 
-    # this rank's frames: pinned host copies (e2e arm) and device copies (kernel arm)
-    host, dev, planes = [], [], []
-    for i in range(NROT):
-        f = make_frame(H, W, NC, PREC, args.kind, seed=rank * NROT + i)
+    # this rank's shard of the sequence: frame f of the job goes to rank f % world (no data-path collective)
+    mine = shard_frames(F * world, rank, world)
+    host, dev = [], []
+    for f in mine:
         t = torch.empty((H, W, NC), dtype=torch.uint16).pin_memory()
-        t.numpy()[...] = f
+        t.numpy()[...] = make_frame(H, W, NC, PREC, args.kind, seed=f)
         host.append(t)
         dev.append(t.cuda())
-        planes.append(j2k.planes_of(t.numpy()))
+    back = [torch.empty((H, W, NC), dtype=torch.uint16).pin_memory() for _ in range(F)]   # decoded frames, e2e arm
+    back_dev = [torch.empty((H, W, NC), dtype=torch.uint16, device="cuda") for _ in range(F)]
     torch.cuda.synchronize()
-    out = C.POINTER(C.c_uint8)()
-    n = C.c_size_t(0)
-    ms = (C.c_float * 8)()
-    cnt = (C.c_uint64 * 6)()
 
-    lib.j2kcuda_decoder_create.restype = C.c_void_p
-    dec = C.c_void_p(lib.j2kcuda_decoder_create(local))
-    if not dec.value:
-        raise SystemExit("decoder_create failed: " + L.last_error())
-    back = torch.empty((H, W, NC), dtype=torch.uint16).pin_memory()       # decoded frame lands here (e2e arm)
-    back_planes = j2k.planes_of(back.numpy())
-    dms = (C.c_float * 8)()
-    tdec = [0.0]
+    def plane_table(arrays):
+        keep = [j2k.planes_of(a) for a in arrays]
+        tab = (C.POINTER(L.Plane) * len(keep))(*[C.cast(k, C.POINTER(L.Plane)) for k in keep])
+        return tab, keep
 
-    def step_device(i):
-        """encode a frame that is resident in HBM, decode the codestream, leave the pixels in HBM"""
-        d = dev[i % NROT]
-        rc = lib.j2kcuda_encoder_set_device_input(enc, C.c_void_p(d.data_ptr()), C.c_int64(W * NC * 2), L.USHORT)
-        rc = rc or lib.j2kcuda_encoder_run(enc)
-        rc = rc or lib.j2kcuda_encoder_finish(enc, C.byref(out), C.byref(n))
-        t0 = time.perf_counter()
-        rc = rc or lib.j2kcuda_decoder_prepare(dec, out, n, 0)
-        rc = rc or lib.j2kcuda_decoder_run(dec)
-        tdec[0] += time.perf_counter() - t0
+    def dev_table(tensors):
+        keep = []
+        for t in tensors:
+            pl = (L.Plane * 1)()
+            pl[0].buf = t.data_ptr(); pl[0].colbytes = NC * 2; pl[0].rowbytes = W * NC * 2
+            pl[0].width = W; pl[0].height = H; pl[0].sample_type = L.USHORT
+            keep.append(pl)
+        tab = (C.POINTER(L.Plane) * len(keep))(*[C.cast(k, C.POINTER(L.Plane)) for k in keep])
+        return tab, keep
+
+    host_in, _k1 = plane_table([t.numpy() for t in host])
+    host_out, _k2 = plane_table([t.numpy() for t in back])
+    dev_in, _k3 = dev_table(dev)
+    dev_out, _k4 = dev_table(back_dev)
+
+    lib.j2kcuda_sequence_create.restype = C.c_void_p
+    seq = C.c_void_p(lib.j2kcuda_sequence_create(C.byref(p), local, args.workers))
+    if not seq.value:
+        raise SystemExit("sequence_create failed: " + L.last_error())
+    outs = (C.POINTER(C.c_uint8) * F)()
+    lens = (C.c_size_t * F)()
+
+    def step(flags, tin, tout):
+        """encode the batch, decode the codestreams it produced"""
+        rc = lib.j2kcuda_sequence_encode(seq, tin, F, NC, flags, outs, lens)
         if rc:
-            raise SystemExit("step failed: " + L.last_error())
-        lib.j2kcuda_free(out)
-        return n.value
-
-    def step_host(i):
-        """the same through the reference-facing calls with pinned host buffers on both sides"""
-        rc = lib.j2kcuda_encoder_upload(enc, planes[i % NROT], NC)
-        rc = rc or lib.j2kcuda_encoder_run(enc)
-        rc = rc or lib.j2kcuda_encoder_finish(enc, C.byref(out), C.byref(n))
+            raise SystemExit("sequence_encode failed: " + L.last_error())
         t0 = time.perf_counter()
-        rc = rc or lib.j2kcuda_decoder_prepare(dec, out, n, 0)
-        rc = rc or lib.j2kcuda_decoder_run(dec)
-        rc = rc or lib.j2kcuda_decoder_download(dec, back_planes, NC)
-        tdec[0] += time.perf_counter() - t0
+        rc = lib.j2kcuda_sequence_decode(seq, C.cast(outs, C.POINTER(C.POINTER(C.c_uint8))), lens, F, 0, tout, NC, flags)
         if rc:
-            raise SystemExit("step failed: " + L.last_error())
-        lib.j2kcuda_free(out)
-        return n.value
+            raise SystemExit("sequence_decode failed: " + L.last_error())
+        dt = time.perf_counter() - t0
+        nbytes = sum(lens[i] for i in range(F))
+        for i in range(F):
+            lib.j2kcuda_free(outs[i])
+        return nbytes, dt
 
-    def timed(step):
-        for i in range(args.warmup):
-            step(i)
+    def stats(reset):
+        em, dm = (C.c_double * 8)(), (C.c_double * 8)()
+        ec, dc = (C.c_uint64 * 6)(), (C.c_uint64 * 6)()
+        fr = (C.c_uint64 * 2)()
+        lib.j2kcuda_sequence_stats(seq, em, ec, dm, dc, fr, 1 if reset else 0)
+        return np.array(list(em)), list(ec), np.array(list(dm)), list(dc), list(fr)
+
+    def timed(flags, tin, tout):
+        for _ in range(args.warmup):
+            step(flags, tin, tout)
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
+        stats(True)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        acc = np.zeros(8)
-        dacc = np.zeros(7)
-        tdec[0] = 0.0
-        launches = nbytes = d2h = 0
+        nbytes, tdec = 0, 0.0
         torch.cuda.synchronize()
         e0.record()
-        for i in range(args.steps):
-            nbytes += step(i)
-            lib.j2kcuda_encoder_timings(enc, ms, 8)
-            lib.j2kcuda_encoder_counters(enc, cnt, 6)
-            acc += np.array(list(ms))
-            launches += cnt[0]
-            d2h = cnt[5]
-            lib.j2kcuda_decoder_timings(dec, dms, 7)
-            lib.j2kcuda_decoder_counters(dec, cnt, 6)
-            dacc += np.array(list(dms)[:7])
-            launches += cnt[0]
+        for _ in range(args.steps):
+            nb, dt = step(flags, tin, tout)
+            nbytes += nb
+            tdec += dt
         e1.record()
         torch.cuda.synchronize()
         t = torch.tensor([e0.elapsed_time(e1)], device="cuda")
         if world > 1:
             dist.barrier()
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item()), acc / args.steps, launches, nbytes / args.steps, d2h, dacc / args.steps, tdec[0] / args.steps * 1e3
+        return float(t.item()), nbytes / (args.steps * F), tdec / args.steps * 1e3, stats(True)
 
     sampler = ClockSampler(local)
     sampler.start()
-    t_dev, st_dev, launches, cs_bytes, d2h_dev, dst_dev, dec_ms_dev = timed(step_device)
-    t_e2e, st_e2e, _, _, d2h_e2e, dst_e2e, dec_ms_e2e = timed(step_host)
-    if not np.array_equal(back.numpy(), host[(args.steps - 1) % NROT].numpy()):
-        raise SystemExit("round trip is not lossless")
+    t_dev, cs_bytes, dec_ms_dev, st_dev = timed(1, dev_in, dev_out)          # J2KCUDA_SEQ_DEVICE_PIXELS
+    for i in range(F):
+        if not torch.equal(back_dev[i], dev[i]):
+            raise SystemExit("device round trip of frame %d is not lossless" % i)
+    t_e2e, _, dec_ms_e2e, st_e2e = timed(0, host_in, host_out)
+    for i in range(F):
+        if not np.array_equal(back[i].numpy(), host[i].numpy()):
+            raise SystemExit("round trip of frame %d is not lossless" % i)
     sampler.stop = True
     sampler.join(timeout=3)
+    lib.j2kcuda_sequence_destroy(seq)
 
-    lib.j2kcuda_encoder_counters(enc, cnt, 6)
-    nblocks, nsym = int(cnt[1]), int(cnt[2])
-    lib.j2kcuda_encoder_destroy(enc)
-    lib.j2kcuda_decoder_destroy(dec)
+    # the roofline kernel timed alone: one context, frames one after the other (nothing else on the device),
+    # CUDA events recorded by the library on the context's own stream around the level-1 launch
+    solo = C.c_void_p(lib.j2kcuda_sequence_create(C.byref(p), local, 1))
+    for _ in range(2):
+        step_solo = lib.j2kcuda_sequence_encode(solo, dev_in, F, NC, 1, outs, lens)
+        if step_solo:
+            raise SystemExit("solo pass failed: " + L.last_error())
+        lib.j2kcuda_sequence_decode(solo, C.cast(outs, C.POINTER(C.POINTER(C.c_uint8))), lens, F, 0, dev_out, NC, 1)
+        for i in range(F):
+            lib.j2kcuda_free(outs[i])
+        em, ec, dm, dc, fr = (C.c_double * 8)(), (C.c_uint64 * 6)(), (C.c_double * 8)(), (C.c_uint64 * 6)(), (C.c_uint64 * 2)()
+        lib.j2kcuda_sequence_stats(solo, em, ec, dm, dc, fr, 1)
+    lib.j2kcuda_sequence_destroy(solo)
+    solo_enc, solo_dec, solo_n = np.array(list(em)) / fr[0], np.array(list(dm)) / fr[1], int(fr[0])
     if rank != 0:
         return
+
+    em_b, ec_b, dm_b, dc_b, fr_b = st_dev
+    em_e, ec_e, dm_e, dc_e, fr_e = st_e2e
+    nfr = max(int(fr_b[0]), 1)
     mpix = W * H / 1e6
-    value = world * args.steps * mpix / (t_dev * 1e-3)
-    e2e = world * args.steps * mpix / (t_e2e * 1e-3)
+    value = world * args.steps * F * mpix / (t_dev * 1e-3)
+    e2e = world * args.steps * F * mpix / (t_e2e * 1e-3)
     peak, peak_src = peaks()
     l1_bytes = 8.0 * W * H * NC                      # 4 B read + 4 B written per sample, level 1 of every component
-    l1_ms = float(st_dev[7])
+    l1_ms = float(solo_enc[7])
     achieved = l1_bytes / (l1_ms * 1e-3) / 1e9
+    l1_ms_batch = float(em_b[7]) / nfr
+    il1_ms = float(solo_dec[6])
+    nblocks, nsym = int(ec_b[1]) // nfr, int(ec_b[2]) // nfr
+    enc_names = ["upload", "mct", "dwt", "t1_context", "t1_mq", "compact_d2h", "host_t2", "dwt_l1"]
+    dec_names = ["host_parse", "h2d", "t1", "idwt", "imct_pack", "d2h", "idwt_l1"]
     line = {
         "metric": "4K lossless encode+decode MPix/s", "value": value, "unit": "MPix/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": t_dev / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int32", "data": "synthetic (%s)" % args.kind,
-        "config": {"workload": WORKLOAD, "direction": "encode then decode of the same frame (round trip verified lossless)", "frames_per_step_per_gpu": 1,
-                   "l2": "inputs and planes larger than L2: %d rotating frames" % NROT,
+        "config": {"workload": WORKLOAD, "direction": "encode then decode of the same frames (every round trip verified lossless)",
+                   "frames_per_step_per_gpu": F, "frames_in_flight": args.workers,
+                   "sharding": "frame f of the job -> rank f %% %d, no collective on the data path" % world,
+                   "l2": "inputs larger than L2: %d distinct frames per step (%.0f MB in, %.0f MB of planes each)" % (F, F * W * H * NC * 2 / 1e6, 2 * W * H * NC * 4 / 1e6),
                    "codestream_bytes_per_frame": cs_bytes, "code_blocks_per_frame": nblocks, "mq_symbols_per_frame": nsym},
-        "e2e": {"value": e2e, "unit": "MPix/s", "h2d_bytes_per_step": int(W * H * NC * 2 + cs_bytes), "d2h_bytes_per_step": int(d2h_e2e + W * H * NC * 2),
-                "ms_per_step": t_e2e / args.steps},
-        "gpu_launches": int(launches),
+        "e2e": {"value": e2e, "unit": "MPix/s", "h2d_bytes_per_step": int(F * (W * H * NC * 2 + cs_bytes)),
+                "d2h_bytes_per_step": int(ec_e[5] / args.steps + F * W * H * NC * 2), "ms_per_step": t_e2e / args.steps},
+        "gpu_launches": int(ec_b[0] + dc_b[0]),
         "roofline": {"bound": "hbm", "kernel": "k_dwt_forward<Fwd53> level 1", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": l1_bytes, "avg_launch_ms": l1_ms},
-        "stages_ms": {k: float(v) for k, v in zip(["upload", "mct", "dwt", "t1_context", "t1_mq", "compact_d2h", "host_t2", "dwt_l1"], st_dev)},
-        "decode_stages_ms": {k: float(v) for k, v in zip(["host_parse", "h2d", "t1", "idwt", "imct_pack", "d2h", "idwt_l1"], dst_dev)},
-        "encode_mpix_s": mpix / ((t_dev / args.steps - dec_ms_dev) * 1e-3), "decode_mpix_s": mpix / (dec_ms_dev * 1e-3),
-        "t1": {"code_blocks_per_s": nblocks / ((st_dev[3] + st_dev[4]) * 1e-3), "mq_symbols_per_s": nsym / (st_dev[4] * 1e-3)},
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": TRAFFIC_L1, "peak_source": peak_src + " (burst: kernel timed alone)",
+                     "algorithmic_bytes_per_launch": l1_bytes, "avg_launch_ms": l1_ms, "launches_timed": solo_n,
+                     "how": "library CUDA events on the context's stream around the launch, one frame at a time after the timed region",
+                     "in_batch": {"avg_launch_ms": l1_ms_batch, "achieved": l1_bytes / (l1_ms_batch * 1e-3) / 1e9,
+                                  "note": "same launch inside the timed region, sharing the device with the Tier-1 kernels of the other frames in flight"},
+                     "inverse_level1": {"avg_launch_ms": il1_ms, "achieved": l1_bytes / (il1_ms * 1e-3) / 1e9}},
+        "stages_ms_per_frame_alone": {k: float(v) for k, v in zip(enc_names, solo_enc)},
+        "decode_stages_ms_per_frame_alone": {k: float(v) for k, v in zip(dec_names, solo_dec)},
+        "stages_ms_per_frame_in_batch": {k: float(v) / nfr for k, v in zip(enc_names, em_b)},
+        "decode_stages_ms_per_frame_in_batch": {k: float(v) / nfr for k, v in zip(dec_names, dm_b)},
+        "encode_mpix_s": F * mpix / ((t_dev / args.steps - dec_ms_dev) * 1e-3), "decode_mpix_s": F * mpix / (dec_ms_dev * 1e-3),
+        "e2e_encode_mpix_s": F * mpix / ((t_e2e / args.steps - dec_ms_e2e) * 1e-3), "e2e_decode_mpix_s": F * mpix / (dec_ms_e2e * 1e-3),
+        "t1": {"code_blocks_per_s_alone": nblocks / ((solo_enc[3] + solo_enc[4]) * 1e-3), "mq_symbols_per_s_alone": nsym / (solo_enc[4] * 1e-3),
+               "decode_code_blocks_per_s_alone": nblocks / (solo_dec[2] * 1e-3),
+               "code_blocks_per_s_job": world * args.steps * F * nblocks / (t_dev * 1e-3)},
         "clocks": sampler.summary(),
     }
     if not args.no_cpu_baseline:

@@ -150,11 +150,34 @@ int j2kcuda_decoder_download(j2kcuda_decoder* d, const j2kcuda_plane* planes, in
 /* keep result on device: interleaved u8/u16, `ncomp` samples per pixel */
 int j2kcuda_decoder_get_device_output(j2kcuda_decoder* d, void** d_pixels, int64_t* pitch_bytes,
                                       int* sample_type);
+/* copy the decoded interleaved image into caller-owned DEVICE memory (rows `pitch_bytes` apart) */
+int j2kcuda_decoder_copy_to_device(j2kcuda_decoder* d, void* d_pixels, int64_t pitch_bytes);
 /* [0] host tier-2 parse (wall) [1] H2D [2] t1 [3] idwt [4] imct+pack [5] D2H [6] idwt finest level */
 int j2kcuda_decoder_timings(j2kcuda_decoder* d, float* ms, int n);
 int j2kcuda_decoder_counters(j2kcuda_decoder* d, uint64_t* v, int n);
 
-/* ---- batches: frames of a sequence on this process's device (one process per GPU) --------- */
+/* ---- sequences: frames of an image sequence on this process's device (one process per GPU;
+ *      configs C4/C5).  Frames are independent, so a sequence keeps `nworkers` contexts (own CUDA
+ *      stream + buffers + host thread each): host Tier-2 of one frame overlaps the kernels of the
+ *      others.  What FrameSeq's per-frame loop (src/aftereffects/FrameSeq.cpp) would call once per
+ *      render batch instead of once per frame. ------------------------------------------------ */
+typedef struct j2kcuda_sequence j2kcuda_sequence;
+enum { J2KCUDA_SEQ_DEVICE_PIXELS = 1 };  /* frames[i][0].buf is a DEVICE pointer to interleaved pixels,
+                                            rowbytes = pitch; ncomp samples per pixel */
+/* p may be NULL for a decode-only sequence; device < 0 = p->device / current; nworkers 0 -> 4 */
+j2kcuda_sequence* j2kcuda_sequence_create(const j2kcuda_params* p, int device, int nworkers);
+void j2kcuda_sequence_destroy(j2kcuda_sequence* s);
+int j2kcuda_sequence_encode(j2kcuda_sequence* s, const j2kcuda_plane* const* frames, int nframes,
+                            int nplanes, unsigned flags, uint8_t** outs, size_t* out_lens);
+int j2kcuda_sequence_decode(j2kcuda_sequence* s, const uint8_t* const* streams, const size_t* lens,
+                            int nframes, unsigned reduce, const j2kcuda_plane* const* frames,
+                            int nplanes, unsigned flags);
+/* totals over all frames since the last reset: the per-frame arrays of j2kcuda_encoder_timings /
+ * _counters and j2kcuda_decoder_timings / _counters summed (8 doubles + 6 counters each way),
+ * frames[0] = frames encoded, frames[1] = frames decoded.  Any pointer may be NULL. */
+int j2kcuda_sequence_stats(j2kcuda_sequence* s, double* enc_ms, uint64_t* enc_cnt, double* dec_ms,
+                           uint64_t* dec_cnt, uint64_t* frames, int reset);
+/* one-shot forms (create a sequence, run it, destroy it) */
 int j2kcuda_encode_batch(const j2kcuda_params* p, const j2kcuda_plane* const* frames, int nframes,
                          int nplanes, uint8_t** outs, size_t* out_lens);
 int j2kcuda_decode_batch(const uint8_t* const* streams, const size_t* lens, int nframes,

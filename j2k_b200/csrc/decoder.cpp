@@ -405,19 +405,15 @@ int j2kcuda_decode(const uint8_t* bytes, size_t n, unsigned reduce, const j2kcud
     return rc;
 }
 
-int j2kcuda_decode_batch(const uint8_t* const* streams, const size_t* lens, int nframes, unsigned reduce,
-                         const j2kcuda_plane* const* frames, int nplanes) {
-    if (!streams || !lens || !frames) return set_error(J2KCUDA_ERR_PARAM, "null argument");
-    j2kcuda_decoder* d = j2kcuda_decoder_create(-1);
-    if (!d) return J2KCUDA_ERR_NO_DEVICE;
-    int rc = 0;
-    for (int i = 0; i < nframes && !rc; ++i) {
-        rc = j2kcuda_decoder_prepare(d, streams[i], lens[i], reduce);
-        if (!rc) rc = j2kcuda_decoder_run(d);
-        if (!rc) rc = j2kcuda_decoder_download(d, frames[i], nplanes);
-    }
-    j2kcuda_decoder_destroy(d);
-    return rc;
+int j2kcuda_decoder_copy_to_device(j2kcuda_decoder* d, void* d_pixels, int64_t pitch_bytes) {
+    if (!d || !d_pixels) return set_error(J2KCUDA_ERR_PARAM, "null argument");
+    if (!d->ran) return set_error(J2KCUDA_ERR_PARAM, "decoder_run has not completed");
+    const size_t row = (size_t)d->outW * d->ncomp * d->S;
+    if (pitch_bytes < (int64_t)row) return set_error(J2KCUDA_ERR_PARAM, "destination pitch smaller than a decoded row");
+    CK(cudaSetDevice(d->device));
+    CK(cudaMemcpy2DAsync(d_pixels, (size_t)pitch_bytes, d->d_out, row, row, (size_t)d->outH, cudaMemcpyDeviceToDevice, d->st));
+    CK(cudaStreamSynchronize(d->st));
+    return J2KCUDA_OK;
 }
 
 int j2kcuda_t2_parse(const uint8_t* bytes, size_t n, unsigned reduce, int32_t** blkinfo, int* nblocks, uint8_t** seg, size_t* seg_len) {

@@ -2,6 +2,9 @@
 // Reference behaviour: ext/grok/src/lib/openjp2/j2k.cpp (setup_encoder :5842-6216, cinema
 // :5623-5778, update_rates :4355-4482, markers :1871-4340, tile parts :9983-10336),
 // tcd.cpp:165-417 (pcrd_bisect / makelayer), t2.cpp:241-384,614-829 (packets).
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include "t2.h"
 #include "../../include/j2kcuda.h"
 #include <algorithm>
@@ -446,12 +449,22 @@ static void write_main_header(const CodingParams& cp, int total_tile_parts, std:
 
 bool EncoderHost::assemble(std::vector<EncTile>& tiles, std::vector<uint8_t>& out, std::string& err) {
     const int nt = (int)(cp.tw * cp.th);
+    auto tS = std::chrono::steady_clock::now();
     if ((int)tiles.size() != nt) { err = "tile count mismatch"; return false; }
     std::vector<std::vector<TilePart>> parts(nt);
     int total_tp = 0;
     for (int i = 0; i < nt; ++i) { tile_parts(cp, tiles[i].geo, parts[i]); total_tp += (int)parts[i].size(); }
     size_t tlm_pos = 0;
     out.clear();
+    {
+        // one allocation for the whole codestream: kept code-block bytes + headers
+        size_t est = 65536;
+        for (auto& t : tiles) {
+            for (auto& b : t.blocks) if (b.totalpasses > 0) est += (size_t)b.rates[b.totalpasses - 1] + 8;
+            est += t.blocks.size() * 4 + 4096;
+        }
+        out.reserve(est);
+    }
     write_main_header(cp, total_tp, out, tlm_pos);
     const bool cinema = tlm_pos != 0;
     // j2k.cpp:4355-4449: layer rates (compression ratios) -> byte budgets per tile
@@ -490,7 +503,9 @@ bool EncoderHost::assemble(std::vector<EncTile>& tiles, std::vector<uint8_t>& ou
         bool any_rate = false;
         for (int k = 0; k < cp.numlayers; ++k) any_rate |= rates[k] > 0.0;
         if (!any_rate) len = ~(uint64_t)0 >> 1;
+        auto tA = std::chrono::steady_clock::now();
         pcrd_bisect(cp, t, parts[i], rates, len);
+        if (getenv("J2KCUDA_T2_TIMING")) fprintf(stderr, "pcrd %.2f ms\n", std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - tA).count());
         t.packno = 0;
         for (size_t tp = 0; tp < parts[i].size(); ++tp) {
             size_t sot = out.size();
@@ -514,6 +529,7 @@ bool EncoderHost::assemble(std::vector<EncTile>& tiles, std::vector<uint8_t>& ou
             if (cinema) { put(tlm, i, 1); put(tlm, psot, 4); }                     // :974-992
         }
     }
+    if (getenv("J2KCUDA_T2_TIMING")) fprintf(stderr, "assemble total %.2f ms\n", std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - tS).count());
     put(out, 0xffd9, 2);                                                           // EOC
     if (cinema) std::copy(tlm.begin(), tlm.end(), out.begin() + (long)tlm_pos);
     return true;

@@ -27,3 +27,20 @@ def make_frame(h, w, ncomp, prec, kind="smooth", seed=0):
             out[..., c] = np.clip(v, 0, top).astype(dt)
         return out
     raise ValueError(kind)
+
+
+def shard_frames(nframes, rank, world):
+    """Frames of a sequence are independent: frame f goes to rank f % world.  -> this rank's frame indices"""
+    if world < 1 or not (0 <= rank < world):
+        raise ValueError("bad rank/world")
+    return list(range(rank, nframes, world))
+
+
+def shard_tiles(ntiles, rank, world):
+    """Tiles of one large frame never read across a tile edge (tcd.cpp:508-526): contiguous runs of tiles per rank,
+    so each rank's tile-parts concatenate in codestream order.  -> (first, last+1)"""
+    if world < 1 or not (0 <= rank < world):
+        raise ValueError("bad rank/world")
+    base, extra = divmod(ntiles, world)
+    first = rank * base + min(rank, extra)
+    return first, first + base + (1 if rank < extra else 0)
