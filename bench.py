@@ -29,10 +29,10 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 W, H, NC, PREC = 4096, 2160, 4, 16
 WORKLOAD = "4096x2160 16-bit RGBA lossless 5/3 (RCT, 6 resolutions, 64x64 code-blocks, 1 tile)"
-FRAMES = 8   # frames per step per GPU (one batch of the image sequence): 8 x 70.8 MB of input and 283 MB of
+FRAMES = 16  # frames per step per GPU (one batch of the image sequence): 16 x 70.8 MB of input and 283 MB of
              # planes per frame in flight -- far beyond the 126 MB L2, so no flush is needed between steps
 TRAFFIC_L1 = None   # dram bytes per level-1 launch from the ncu --set full capture (profiles/), filled in when captured
-WORKERS = 4  # contexts (stream + buffers + host thread) the sequence keeps in flight
+WORKERS = 8  # contexts (stream + buffers + host thread) the sequence keeps in flight
 
 
 def peaks():

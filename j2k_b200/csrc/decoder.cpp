@@ -182,6 +182,10 @@ static int prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned 
     memset(d->h_seg + seg, 0xff, 32);          // the word-wise MQ reader looks up to 24 bytes past a segment
     seg += 32;
     d->seg_bytes = seg;
+    // longest code-blocks first: a block's decode time follows its byte count, and the warps that get the
+    // long blocks of the low-frequency bands last would otherwise run on alone at the end of the launch
+    std::stable_sort(d->h_blocks.begin(), d->h_blocks.end(),
+                     [](const T1DecBlock& a, const T1DecBlock& b) { return a.data_len > b.data_len; });
     // ---- DWT job tables ----
     std::vector<DwtJob> all;
     d->level_off.assign(levels, 0); d->level_items.assign(levels, 0); d->level_seg.assign(levels, 0);

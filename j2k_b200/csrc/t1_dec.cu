@@ -23,13 +23,14 @@ __global__ void __launch_bounds__(32 * DEC_WARPS, MINB)
 k_t1_decode(const T1DecBlock* __restrict__ blocks, int nblocks, const T1Tables* __restrict__ tab,
             const uint8_t* __restrict__ seg_arena, int raw_output) {
     __shared__ DRows s_rows[DEC_WARPS];
-    __shared__ uint8_t s_state[DEC_WARPS][32];
+    __shared__ ColBuf s_cols[DEC_WARPS];
+    __shared__ uint32_t s_state[DEC_WARPS][32];
     __shared__ uint8_t s_zc[4 * 512];
     __shared__ uint8_t s_sc[256];
     __shared__ uint32_t s_mq[96];
     for (int i = threadIdx.x; i < 2048; i += blockDim.x) s_zc[i] = tab->zc9[i];
     for (int i = threadIdx.x; i < 256; i += blockDim.x) s_sc[i] = tab->sc[i];
-    if (threadIdx.x < 94) s_mq[threadIdx.x] = tab->mq[threadIdx.x];
+    if (threadIdx.x < 94) s_mq[threadIdx.x] = mq_state_word(tab->mq, threadIdx.x);
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int bi = blockIdx.x * DEC_WARPS + warp;
@@ -46,18 +47,19 @@ k_t1_decode(const T1DecBlock* __restrict__ blocks, int nblocks, const T1Tables* 
         u64* z = reinterpret_cast<u64*>(&R);
         for (int i = lane; i < (int)(sizeof(DRows) / sizeof(u64)); i += 32) z[i] = 0;
     }
-    uint8_t* st = s_state[warp];
-    if (lane < T1_NCTX) st[lane] = lane == CTX_UNI ? 46 * 2 : (lane == CTX_AGG ? 3 * 2 : (lane == CTX_ZC ? 4 * 2 : 0));
+    uint32_t* st = s_state[warp];
+    if (lane < T1_NCTX) st[lane] = s_mq[lane == CTX_UNI ? 46 * 2 : (lane == CTX_AGG ? 3 * 2 : (lane == CTX_ZC ? 4 * 2 : 0))];
     __syncwarp();
-    decode_block(blk, R, st, s_zc, s_sc, s_mq, seg_arena, raw_output, lane, 32);
+    decode_block(blk, R, s_cols[warp], st, s_zc, s_sc, s_mq, seg_arena, raw_output, lane, 32);
 }
 
 }  // namespace
 
 void launch_t1_decode(const T1DecBlock* d_blocks, int nblocks, const uint8_t* seg_arena, int raw_output, cudaStream_t st) {
     if (nblocks <= 0) return;
-    // register budget / occupancy trade-off, tunable for experiments: 4 -> 128 regs, 5 -> 96, 6 -> 80
-    static const int variant = [] { const char* e = getenv("J2KCUDA_DEC_MINB"); return e ? atoi(e) : 4; }();
+    // register budget / occupancy trade-off, tunable for experiments: 4 -> 108 regs (16 warps/SM), 5 -> 96 (20, the
+    // default: best with several frames in flight), 6 -> 80 (24)
+    static const int variant = [] { const char* e = getenv("J2KCUDA_DEC_MINB"); return e ? atoi(e) : 5; }();
     const dim3 grid((nblocks + DEC_WARPS - 1) / DEC_WARPS), block(32 * DEC_WARPS);
     if (variant <= 4) k_t1_decode<4><<<grid, block, 0, st>>>(d_blocks, nblocks, t1_tables_device(), seg_arena, raw_output);
     else if (variant == 5) k_t1_decode<5><<<grid, block, 0, st>>>(d_blocks, nblocks, t1_tables_device(), seg_arena, raw_output);

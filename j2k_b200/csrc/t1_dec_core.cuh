@@ -10,12 +10,14 @@
 #endif
 #if defined(__CUDA_ARCH__)
 #define J2K_FFSLL(v) __ffsll((long long)(v))
+#define J2K_CLZ(v) __clz((int)(v))
 #define J2K_SYNCWARP() __syncwarp()
 #define J2K_FMUL(a, b) __fmul_rn((a), (b))
 #define J2K_NOINLINE __noinline__
 #else
 #define J2K_NOINLINE
 #define J2K_FFSLL(v) __builtin_ffsll((long long)(v))
+#define J2K_CLZ(v) __builtin_clz((unsigned)(v))
 #define J2K_SYNCWARP() ((void)0)
 #define J2K_FMUL(a, b) ((a) * (b))
 #endif
@@ -58,35 +60,40 @@ struct MqDec {
         bytein();
         c <<= 7; ct -= 7; a = 0x8000u;
     }
-    J2K_HD inline void renorm() {
+    J2K_HD inline void renorm() {                         // a < 0x8000: shift until bit 15 is set, refilling c
+        uint32_t n = (uint32_t)J2K_CLZ(a) - 16u;
         do {
             if (ct == 0) bytein();
-            a <<= 1; c <<= 1; --ct;
-        } while (a < 0x8000u);
+            const uint32_t k = n < ct ? n : ct;
+            a <<= k; c <<= k; ct -= k; n -= k;
+        } while (n);
     }
-    // st: per-context state (index*2 + mps), tab: T1Tables::mq
-    // (kept out of line on the device: the decision loop has a dozen call sites and must stay inside
-    // the instruction cache)
-    J2K_HD inline uint32_t decode(uint8_t* st, const uint32_t* tab, uint32_t ctx) {   // mqc.cpp:577-595
-        const uint32_t s = st[ctx], e = tab[s], qe = e & 0xffffu;
-        uint32_t d = s & 1u;
+    // st: per-context state WORD = the probability-table entry of the context's current state with the
+    // MPS in bit 15 (Qe uses 15 bits): qe | mps << 15 | next-if-MPS << 16 | next-if-LPS << 24; tab = that
+    // table (mq_state_words).  One shared-memory look-up per decision, a second only when the state moves.
+    J2K_HD inline uint32_t decode(uint32_t* st, const uint32_t* tab, uint32_t ctx) {   // mqc.cpp:577-595
+        const uint32_t e = st[ctx], qe = e & 0x7fffu;
+        uint32_t d = (e >> 15) & 1u;
         a -= qe;
         if ((c >> 16) < qe) {
-            if (a < qe) st[ctx] = (uint8_t)((e >> 16) & 0xffu);
-            else { d ^= 1u; st[ctx] = (uint8_t)(e >> 24); }
+            if (a < qe) st[ctx] = tab[(e >> 16) & 0xffu];
+            else { d ^= 1u; st[ctx] = tab[e >> 24]; }
             a = qe;
             renorm();
         } else {
             c -= qe << 16;
             if ((a & 0x8000u) == 0) {
-                if (a < qe) { d ^= 1u; st[ctx] = (uint8_t)(e >> 24); }
-                else st[ctx] = (uint8_t)((e >> 16) & 0xffu);
+                if (a < qe) { d ^= 1u; st[ctx] = tab[e >> 24]; }
+                else st[ctx] = tab[(e >> 16) & 0xffu];
                 renorm();
             }
         }
         return d;
     }
 };
+
+// state word table from T1Tables::mq (entry s = state index * 2 + mps)
+J2K_HD inline uint32_t mq_state_word(const uint32_t* mq, int s) { return mq[s] | ((uint32_t)(s & 1) << 15); }
 
 J2K_HD inline uint32_t w3(u64 m, int x) {          // bits x-1, x, x+1 of a row
     return (uint32_t)(x ? (m >> (x - 1)) : (m << 1)) & 7u;
@@ -126,10 +133,39 @@ J2K_HD inline uint32_t sc_index(uint32_t s9, uint32_t g9) {
            (((g9 >> 3) & 1u) << 4) | (((g9 >> 5) & 1u) << 5) | (((g9 >> 1) & 1u) << 6) | (((g9 >> 7) & 1u) << 7);
 }
 
+// Per-warp scratch of the stripe being scanned, in column-major form: the row masks are turned into
+// per-column words once per stripe by all lanes in parallel (two columns per lane), the serial decision
+// loop then touches one word per column, and its results go back into the row masks with warp ballots.
+//   win[x]  18-bit significance window of column x (see pack_win)
+//   aux[x]  nibbles: bits 0-3 samples to code in this pass (membership / validity), 4-7 refined
+//   out[x]  nibbles: 0-3 newly significant, 4-7 negative, 8-11 visited, 12-15 decoded magnitude bit
+struct ColBuf {
+    uint32_t win[64];
+    uint32_t aux[64];
+    uint32_t out[64];
+};
+
+// bit `b` of out[x] of all 64 columns as a row mask; o0 / o1 are this lane's out[lane] / out[lane + 32]
+J2K_HD inline u64 rowmask(const uint32_t* out, uint32_t o0, uint32_t o1, int b) {
+#if defined(__CUDA_ARCH__)
+    (void)out;
+    return (u64)__ballot_sync(0xffffffffu, (o0 >> b) & 1u) | ((u64)__ballot_sync(0xffffffffu, (o1 >> b) & 1u) << 32);
+#else
+    (void)o0; (void)o1;
+    u64 m = 0;
+    for (int x = 0; x < 64; ++x) m |= (u64)((out[x] >> b) & 1u) << x;
+    return m;
+#endif
+}
+// nibble -> the window bits of rows 1..4 at column offset 0 (bits 3, 6, 9, 12)
+J2K_HD inline uint32_t spread4(uint32_t n) {
+    return ((n & 1u) << 3) | ((n & 2u) << 5) | ((n & 4u) << 7) | ((n & 8u) << 9);
+}
+
 // Decode one code-block.  Called by all `nlanes` lanes of a warp with identical arguments except `lane`;
 // the decision loop runs redundantly on warp-uniform data, the lane index only partitions the
-// column-parallel parts (fold, final pass).  R and st must be zero / reset on entry.
-J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, uint8_t* st, const uint8_t* zc_all, const uint8_t* sc,
+// column-parallel parts (stripe set-up and write-back, fold, final pass).  R and st must be zero / reset on entry.
+J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uint32_t* st, const uint8_t* zc_all, const uint8_t* sc,
                                 const uint32_t* mqtab, const uint8_t* seg_arena, int raw_output, int lane, int nlanes) {
     const int w = blk.w, h = blk.h;
     int32_t* out = blk.coeff;
@@ -146,60 +182,94 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, uint8_t* st, co
     bool firstfold = true;
     for (int passno = 0; passno < blk.npasses && bp >= 0; ++passno) {
         for (int sidx = 0; sidx < nstripes; ++sidx) {
-            Stripe s;
             const int ib = 4 * sidx;       // smem index of row q = 0
+            u64 S[6], V[4], valid[4];
 #pragma unroll
-            for (int q = 0; q < 6; ++q) { s.S[q] = R.sig[ib + q]; s.G[q] = R.sgn[ib + q]; }
-            u64 valid[4];
+            for (int q = 0; q < 6; ++q) S[q] = R.sig[ib + q];
 #pragma unroll
-            for (int r = 0; r < 4; ++r) {
-                s.V[r] = R.vis[ib + 1 + r]; s.F[r] = R.ref[ib + 1 + r]; s.B[r] = R.bit[ib + 1 + r]; s.L[r] = R.last[ib + 1 + r];
-                valid[r] = (ib + r < h) ? colmask : 0ull;
-            }
+            for (int r = 0; r < 4; ++r) { V[r] = R.vis[ib + 1 + r]; valid[r] = (ib + r < h) ? colmask : 0ull; }
+            // ---- which columns can hold anything to decode in this pass ----
+            u64 memb[4], cols = 0, memall = 0;
             if (passtype == 0) {
-                // significance propagation: only columns that have (or acquire, from the column just
-                // scanned) a significant sample in their 3x6 window can hold candidates
-                u64 active = 0;
+                // significance propagation: columns that have (or acquire, from the column just scanned)
+                // a significant sample in their 3x6 window
 #pragma unroll
-                for (int q = 0; q < 6; ++q) active |= (s.S[q] << 1) | s.S[q] | (s.S[q] >> 1);
-                active &= colmask;
-                u64 donec = 0;
+                for (int q = 0; q < 6; ++q) cols |= (S[q] << 1) | S[q] | (S[q] >> 1);
+                cols &= colmask;
+#pragma unroll
+                for (int r = 0; r < 4; ++r) memb[r] = ~S[r + 1] & valid[r];
+            } else if (passtype == 1) {
+#pragma unroll
+                for (int r = 0; r < 4; ++r) { memb[r] = S[r + 1] & ~V[r] & valid[r]; cols |= memb[r]; }
+            } else {
+#pragma unroll
+                for (int r = 0; r < 4; ++r) { memb[r] = ~S[r + 1] & ~V[r] & valid[r]; cols |= memb[r]; }
+                memall = (ib + 3 < h) ? (memb[0] & memb[1] & memb[2] & memb[3]) : 0ull;
+            }
+            if (cols == 0) {
+                if (passtype == 2 && (V[0] | V[1] | V[2] | V[3])) {
+                    if (lane < 4) R.vis[ib + 1 + lane] = 0;
+                    if (nlanes == 1) { R.vis[ib + 1] = R.vis[ib + 2] = R.vis[ib + 3] = R.vis[ib + 4] = 0; }
+                    J2K_SYNCWARP();
+                }
+                continue;
+            }
+            // ---- column-major set-up, two columns per lane ----
+            for (int x = lane; x < 64; x += nlanes) {
+                cb.win[x] = pack_win(S, x);
+                uint32_t a = nibble(memb, x);
+                if (passtype == 1) a |= nibble(&R.ref[ib + 1], x) << 4;
+                cb.aux[x] = a;
+                cb.out[x] = 0;
+            }
+            J2K_SYNCWARP();
+            bool any = false;
+            int carry_x = -2;
+            uint32_t carry_s = 0, carry_g = 0;
+            if (passtype == 0) {
+                u64 active = cols, donec = 0;
                 while (u64 rem = active & ~donec) {
                     const int x = J2K_FFSLL(rem) - 1;
                     donec |= 1ull << x;
-                    uint32_t win = pack_win(s.S, x), gwin = 0;
+                    uint32_t win = cb.win[x];
+                    if (x == carry_x + 1) win |= carry_s;
+                    const uint32_t mem4 = cb.aux[x];
+                    uint32_t gwin = 0;
                     bool have_g = false;
-                    const uint32_t val4 = nibble(valid, x);
                     uint32_t new4 = 0, neg4 = 0, vis4 = 0;
 #pragma unroll 1
                     for (int r = 0; r < 4; ++r) {
                         const uint32_t s9 = (win >> (3 * r)) & 0x1ffu;
-                        if (!((val4 >> r) & 1u) || (s9 & 0x10u) || !(s9 & 0x1efu)) continue;
+                        if (!((mem4 >> r) & 1u) || !(s9 & 0x1efu)) continue;
                         vis4 |= 1u << r;
                         if (!mq.decode(st, mqtab, zc[s9 & 0x1efu])) continue;
-                        if (!have_g) { gwin = pack_win(s.G, x); have_g = true; }
+                        if (!have_g) {
+                            u64 G[6];
+#pragma unroll
+                            for (int q = 0; q < 6; ++q) G[q] = R.sgn[ib + q];
+                            gwin = pack_win(G, x);
+                            if (x == carry_x + 1) gwin |= carry_g;
+                            have_g = true;
+                        }
                         const uint32_t e = sc[sc_index(s9, (gwin >> (3 * r)) & 0x1ffu)];
                         const uint32_t neg = mq.decode(st, mqtab, CTX_SC + (e & 7u)) ^ (e >> 3);
                         win |= 2u << (3 * r + 3);
                         gwin |= (neg << 1) << (3 * r + 3);
                         new4 |= 1u << r; neg4 |= neg << r;
                     }
-                    if (vis4) scatter(s.V, vis4, x);
+                    if (vis4) { cb.out[x] = new4 | (neg4 << 4) | (vis4 << 8); any = true; }
                     if (new4) {
-                        scatter(s.S + 1, new4, x); scatter(s.G + 1, neg4, x); scatter(s.B, new4, x); scatter(s.L, new4, x);
+                        carry_x = x; carry_s = spread4(new4); carry_g = spread4(neg4);
                         active |= (2ull << x) & colmask;               // the next column may now hold candidates
                     }
                 }
             } else if (passtype == 1) {
                 // magnitude refinement: significant and not coded in this plane's first pass
-                u64 memb[4], cols = 0;
-#pragma unroll
-                for (int r = 0; r < 4; ++r) { memb[r] = s.S[r + 1] & ~s.V[r] & valid[r]; cols |= memb[r]; }
                 while (cols) {
                     const int x = J2K_FFSLL(cols) - 1;
                     cols &= cols - 1;
-                    const uint32_t win = pack_win(s.S, x);
-                    const uint32_t mem4 = nibble(memb, x), ref4 = nibble(s.F, x);
+                    const uint32_t win = cb.win[x];
+                    const uint32_t a = cb.aux[x], mem4 = a & 15u, ref4 = a >> 4;
                     uint32_t bit4 = 0;
 #pragma unroll 1
                     for (int r = 0; r < 4; ++r) {
@@ -208,22 +278,18 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, uint8_t* st, co
                         const uint32_t ctx = ((ref4 >> r) & 1u) ? CTX_MAG + 2 : (s9 ? CTX_MAG + 1 : CTX_MAG);
                         bit4 |= mq.decode(st, mqtab, ctx) << r;
                     }
-                    if (bit4) scatter(s.B, bit4, x);
+                    if (bit4) { cb.out[x] = bit4 << 12; any = true; }
                 }
-#pragma unroll
-                for (int r = 0; r < 4; ++r) { s.L[r] |= memb[r]; s.F[r] |= memb[r]; }
             } else {
                 // cleanup: everything not yet significant and not visited
-                u64 memb[4], cols = 0;
-#pragma unroll
-                for (int r = 0; r < 4; ++r) { memb[r] = ~s.S[r + 1] & ~s.V[r] & valid[r]; cols |= memb[r]; }
-                const u64 memall = (ib + 3 < h) ? (memb[0] & memb[1] & memb[2] & memb[3]) : 0ull;
                 while (cols) {
                     const int x = J2K_FFSLL(cols) - 1;
                     cols &= cols - 1;
-                    uint32_t win = pack_win(s.S, x), gwin = 0;
+                    uint32_t win = cb.win[x];
+                    if (x == carry_x + 1) win |= carry_s;
+                    uint32_t gwin = 0;
                     bool have_g = false;
-                    const uint32_t mem4 = nibble(memb, x);
+                    const uint32_t mem4 = cb.aux[x];
                     int rstart = 0;
                     bool partial = false;
                     if (((memall >> x) & 1ull) && win == 0) {
@@ -240,23 +306,50 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, uint8_t* st, co
                         const uint32_t s9 = (win >> (3 * r)) & 0x1ffu;
                         if (partial) partial = false;                  // the sample that ended the run is significant
                         else if (!mq.decode(st, mqtab, zc[s9 & 0x1efu])) continue;
-                        if (!have_g) { gwin = pack_win(s.G, x); have_g = true; }
+                        if (!have_g) {
+                            u64 G[6];
+#pragma unroll
+                            for (int q = 0; q < 6; ++q) G[q] = R.sgn[ib + q];
+                            gwin = pack_win(G, x);
+                            if (x == carry_x + 1) gwin |= carry_g;
+                            have_g = true;
+                        }
                         const uint32_t e = sc[sc_index(s9, (gwin >> (3 * r)) & 0x1ffu)];
                         const uint32_t neg = mq.decode(st, mqtab, CTX_SC + (e & 7u)) ^ (e >> 3);
                         win |= 2u << (3 * r + 3);
                         gwin |= (neg << 1) << (3 * r + 3);
                         new4 |= 1u << r; neg4 |= neg << r;
                     }
-                    if (new4) { scatter(s.S + 1, new4, x); scatter(s.G + 1, neg4, x); scatter(s.B, new4, x); scatter(s.L, new4, x); }
+                    if (new4) {
+                        cb.out[x] = new4 | (neg4 << 4); any = true;
+                        carry_x = x; carry_s = spread4(new4); carry_g = spread4(neg4);
+                    }
                 }
-#pragma unroll
-                for (int r = 0; r < 4; ++r) s.V[r] = 0;
             }
-            // write the stripe back (rows of the neighbouring stripes are unchanged)
+            J2K_SYNCWARP();
+            // ---- results back into the row masks (rows of the neighbouring stripes are unchanged) ----
+            uint32_t o0 = 0, o1 = 0;
+#if defined(__CUDA_ARCH__)
+            if (any) { o0 = cb.out[lane]; o1 = cb.out[lane + 32]; }
+#endif
 #pragma unroll
             for (int r = 0; r < 4; ++r) {
                 const int i = ib + 1 + r;
-                R.sig[i] = s.S[r + 1]; R.sgn[i] = s.G[r + 1]; R.vis[i] = s.V[r]; R.ref[i] = s.F[r]; R.bit[i] = s.B[r]; R.last[i] = s.L[r];
+                if (passtype == 1) {
+                    u64 bits = any ? rowmask(cb.out, o0, o1, 12 + r) : 0ull;
+                    if (lane == 0) { R.bit[i] |= bits; R.last[i] |= memb[r]; R.ref[i] |= memb[r]; }
+                } else {
+                    u64 nw = 0, ng = 0, vs = 0;
+                    if (any) {
+                        nw = rowmask(cb.out, o0, o1, r); ng = rowmask(cb.out, o0, o1, 4 + r);
+                        if (passtype == 0) vs = rowmask(cb.out, o0, o1, 8 + r);
+                    }
+                    if (lane == 0) {
+                        if (nw) { R.sig[i] = S[r + 1] | nw; R.sgn[i] |= ng; R.bit[i] |= nw; R.last[i] |= nw; }
+                        if (passtype == 0) { if (vs) R.vis[i] = V[r] | vs; }
+                        else R.vis[i] = 0;
+                    }
+                }
             }
             J2K_SYNCWARP();
         }

@@ -21,8 +21,12 @@ extern "C" int t1dec_host_block(const uint8_t* data, int len, int w, int h, int 
     if (!npasses || !numbps || !w || !h) return 0;
     static DRows R;
     memset(&R, 0, sizeof(R));
-    uint8_t st[32] = {0};
-    st[CTX_UNI] = 46 * 2; st[CTX_AGG] = 3 * 2; st[CTX_ZC] = 4 * 2;
-    decode_block(b, R, st, zc9, sc, mq, seg.data(), 1, 0, 1);
+    uint32_t tab[94];
+    for (int i = 0; i < 94; ++i) tab[i] = mq_state_word(mq, i);
+    uint32_t st[32];
+    for (int i = 0; i < 32; ++i) st[i] = tab[0];
+    st[CTX_UNI] = tab[46 * 2]; st[CTX_AGG] = tab[3 * 2]; st[CTX_ZC] = tab[4 * 2];
+    static ColBuf cb;
+    decode_block(b, R, cb, st, zc9, sc, tab, seg.data(), 1, 0, 1);
     return 0;
 }
