@@ -76,7 +76,12 @@ typedef struct j2kcuda_params {
     double   rates[16];          /* tcp_rates: compression ratio per layer, 0 = lossless */
     uint32_t compat;             /* J2KCUDA_COMPAT_* */
     int32_t  device;             /* CUDA ordinal, -1 = current */
-    uint32_t reserved[6];
+    /* Tiles of one very large frame sharded across GPUs (config C4): this context encodes only tiles
+     * [tile_first, tile_first + tile_count) of the frame and returns their tile-parts alone (no main
+     * header, no EOC); j2kcuda_join_tile_streams() puts the fragments of all ranks together.
+     * tile_count == 0: the whole frame, a complete codestream. */
+    uint32_t tile_first, tile_count;
+    uint32_t reserved[4];
 } j2kcuda_params;
 
 /* What GetFileInfo needs from the main header (j2k_openjpeg_codec.cpp:222-429). */
@@ -182,6 +187,15 @@ int j2kcuda_encode_batch(const j2kcuda_params* p, const j2kcuda_plane* const* fr
                          int nplanes, uint8_t** outs, size_t* out_lens);
 int j2kcuda_decode_batch(const uint8_t* const* streams, const size_t* lens, int nframes,
                          unsigned reduce, const j2kcuda_plane* const* frames, int nplanes);
+
+/* ---- one frame whose tiles were encoded on several GPUs ----------------------------------- */
+/* p describes the whole frame (tile_count ignored).  frags[i] are the fragments returned by encoders
+ * created with tile ranges that together cover every tile exactly once, in any order; the result
+ * is byte-identical to the codestream one context would have written for the whole frame
+ * (tile-parts are self-delimiting: Psot, j2k.cpp:3826-3862).  Cinema profiles (TLM) are not
+ * joinable.  *out is malloc'd. */
+int j2kcuda_join_tile_streams(const j2kcuda_params* p, const uint8_t* const* frags, const size_t* lens,
+                              int nfrags, uint8_t** out, size_t* out_len);
 
 /* ---- stage entry points (host arrays in/out; what the parity tests drive, one stage at a
  *      time, the way ext/grok's OPJ_PLUGIN_STATE_DEBUG_ENCODE cross-check does) -------------- */

@@ -27,7 +27,8 @@ class Params(C.Structure):
                 ("tile_h", C.c_uint32), ("numlayers", C.c_uint32), ("profile", C.c_uint32),
                 ("max_comp_size", C.c_uint32), ("max_cs_size", C.c_uint64),
                 ("rates", C.c_double * 16), ("compat", C.c_uint32), ("device", C.c_int32),
-                ("reserved", C.c_uint32 * 6)]
+                ("tile_first", C.c_uint32), ("tile_count", C.c_uint32),
+                ("reserved", C.c_uint32 * 4)]
 
 
 class Info(C.Structure):

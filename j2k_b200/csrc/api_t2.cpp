@@ -30,6 +30,7 @@ int j2kcuda_t2_block_count(const j2kcuda_params* p) {
     setup_coding_params(*p, cp);
     int n = 0;
     for (int t = 0; t < (int)(cp.tw * cp.th); ++t) {
+        if (!cp.tile_in_range(t)) continue;
         TileGeo g;
         build_tile(cp, t, 1.0f, g);
         n += (int)g.cblks.size();
@@ -43,6 +44,7 @@ int j2kcuda_t2_block_geometry(const j2kcuda_params* p, int32_t* geo, int max_blo
     setup_coding_params(*p, cp);
     int n = 0;
     for (int t = 0; t < (int)(cp.tw * cp.th); ++t) {
+        if (!cp.tile_in_range(t)) continue;
         TileGeo g;
         build_tile(cp, t, 1.0f, g);
         for (auto& cb : g.cblks) {
@@ -69,6 +71,7 @@ int j2kcuda_t2_assemble(const j2kcuda_params* p, const j2kcuda_block_result* blo
     std::vector<EncTile> tiles(nt);
     int k = 0;
     for (int t = 0; t < nt; ++t) {
+        if (!host.cp.tile_in_range(t)) continue;
         init_enc_tile(host.cp, t, tiles[t]);
         for (auto& b : tiles[t].blocks) {
             if (k >= nblocks) return set_error(J2KCUDA_ERR_PARAM, "too few block results");
@@ -81,6 +84,21 @@ int j2kcuda_t2_assemble(const j2kcuda_params* p, const j2kcuda_block_result* blo
     std::vector<uint8_t> cs;
     std::string err;
     if (!host.assemble(tiles, cs, err)) return set_error(J2KCUDA_ERR_PARAM, err);
+    *out = (uint8_t*)malloc(cs.size() ? cs.size() : 1);
+    if (!*out) return set_error(J2KCUDA_ERR_NOMEM, "malloc");
+    memcpy(*out, cs.data(), cs.size());
+    *out_len = cs.size();
+    return J2KCUDA_OK;
+}
+
+int j2kcuda_join_tile_streams(const j2kcuda_params* p, const uint8_t* const* frags, const size_t* lens, int nfrags,
+                              uint8_t** out, size_t* out_len) {
+    if (!p || !frags || !lens || !out || !out_len || nfrags < 0) return set_error(J2KCUDA_ERR_PARAM, "null argument");
+    CodingParams cp;
+    setup_coding_params(*p, cp);
+    std::vector<uint8_t> cs;
+    std::string err;
+    if (!join_tile_streams(cp, frags, lens, nfrags, cs, err)) return set_error(J2KCUDA_ERR_PARAM, err);
     *out = (uint8_t*)malloc(cs.size() ? cs.size() : 1);
     if (!*out) return set_error(J2KCUDA_ERR_NOMEM, "malloc");
     memcpy(*out, cs.data(), cs.size());

@@ -57,6 +57,7 @@ struct j2kcuda_encoder {
     uint8_t* h_packed = nullptr; size_t h_packed_cap = 0;   // pinned
     std::vector<std::vector<double>> dist;           // per block cumulative distortion
     int mq_lanes = 32;
+    int row0 = 0, row1 = 0;    // image rows covered by this context's tiles (all rows unless a tile range is set)
     // timing
     cudaEvent_t ev[10];
     float ms[8] = {0};
@@ -112,9 +113,12 @@ static int setup_encoder(j2kcuda_encoder* e) {
     const int levels = e->numres - 1;
     e->level_jobs.assign(levels, {});
     size_t sym_units = 0, out_off = 0;
+    e->row0 = e->H; e->row1 = 0;
     for (int t = 0; t < nt; ++t) {
+        if (!cp.tile_in_range(t)) continue;           // another rank's tile (tile ranges, config C4)
         init_enc_tile(cp, t, e->tiles[t]);
         const TileGeo& g = e->tiles[t].geo;
+        e->row0 = std::min(e->row0, g.comps[0].r.y0); e->row1 = std::max(e->row1, g.comps[0].r.y1);
         for (int c = 0; c < e->ncomp; ++c) {
             const CompGeo& cg = g.comps[c];
             const size_t origin = (size_t)cg.r.y0 * e->pitch + cg.r.x0;
@@ -222,8 +226,8 @@ static int upload_planes(j2kcuda_encoder* e, const j2kcuda_plane* planes, int np
             return set_error(J2KCUDA_ERR_PARAM, "plane size differs from the image size");
         if (sample_bytes_of(pl.sample_type) != S || pl.colbytes < S || pl.rowbytes < 0)
             return set_error(J2KCUDA_ERR_PARAM, "planes must share one sample type and have positive strides");
-        const uint8_t* lo = (const uint8_t*)pl.buf;
-        const uint8_t* hi = lo + (size_t)(e->H - 1) * pl.rowbytes + (size_t)(e->W - 1) * pl.colbytes + S;
+        const uint8_t* lo = (const uint8_t*)pl.buf + (size_t)e->row0 * pl.rowbytes;     // only the rows of this context's tiles
+        const uint8_t* hi = (const uint8_t*)pl.buf + (size_t)(e->row1 - 1) * pl.rowbytes + (size_t)(e->W - 1) * pl.colbytes + S;
         ranges.push_back({lo, hi, 0});
     }
     // merge overlapping / adjacent ranges
@@ -276,9 +280,9 @@ static int upload_planes(j2kcuda_encoder* e, const j2kcuda_plane* planes, int np
     e->src.sample_bytes = S;
     e->src.sgnd = planes[0].sgnd;
     for (int c = 0; c < e->ncomp; ++c) {
-        const uint8_t* lo = (const uint8_t*)planes[c].buf;
-        for (auto& m : merged)
-            if (lo >= m.lo && lo < m.hi) { e->src.base[c] = e->d_pix + m.dev + (lo - m.lo); break; }
+        const uint8_t* lo = (const uint8_t*)planes[c].buf + (size_t)e->row0 * planes[c].rowbytes;
+        for (auto& m : merged)          // base = where row 0 would be (rows above row0 are never touched)
+            if (lo >= m.lo && lo < m.hi) { e->src.base[c] = e->d_pix + m.dev + (lo - m.lo) - (size_t)e->row0 * planes[c].rowbytes; break; }
         e->src.colbytes[c] = planes[c].colbytes;
         e->src.rowbytes[c] = planes[c].rowbytes;
         const int depth = planes[c].depth ? planes[c].depth : e->mp.prec[c];
@@ -341,7 +345,18 @@ int j2kcuda_encoder_run(j2kcuda_encoder* e) {
     cudaStream_t st = e->st;
     uint64_t launches = 0;
     CK(cudaEventRecord(e->ev[0], st));
-    launch_mct_forward(e->src, e->mp, e->planeA, st); ++launches;
+    {
+        // only the image rows this context's tiles cover (all of them unless a tile range is set)
+        PixelSrc src = e->src;
+        MctParams mp = e->mp;
+        int32_t* planes[4] = {nullptr, nullptr, nullptr, nullptr};
+        for (int c = 0; c < e->ncomp; ++c) {
+            src.base[c] = e->src.base[c] + (int64_t)e->row0 * e->src.rowbytes[c];
+            planes[c] = e->planeA[c] + (size_t)e->row0 * e->pitch;
+        }
+        mp.height = e->row1 - e->row0;
+        if (mp.height > 0) { launch_mct_forward(src, mp, planes, st); ++launches; }
+    }
     CK(cudaEventRecord(e->ev[1], st));
     const int levels = e->numres - 1;
     for (int l = 0; l < levels; ++l) {
@@ -399,7 +414,7 @@ int j2kcuda_encoder_finish(j2kcuda_encoder* e, uint8_t** out, size_t* out_len) {
     if (!e->ran) return set_error(J2KCUDA_ERR_PARAM, "encoder_run has not completed");
     auto t0 = std::chrono::steady_clock::now();
     const CodingParams& cp = e->cp;
-    for (auto& t : e->tiles) init_enc_tile(cp, t.geo.tileno, t);
+    for (size_t t = 0; t < e->tiles.size(); ++t) if (cp.tile_in_range((int)t)) init_enc_tile(cp, (int)t, e->tiles[t]);
     for (int i = 0; i < e->nblocks; ++i) {
         const T1Result& r = e->h_results[i];
         EncTile& tile = e->tiles[e->blk_tile[i]];

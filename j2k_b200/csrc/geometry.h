@@ -48,6 +48,8 @@ struct CodingParams {         // opj_cp_t + opj_tcp_t subset
     uint64_t max_cs_size = 0;
     uint32_t max_comp_size = 0;
     int compat = 0;
+    uint32_t tile_first = 0, tile_count = 0;   // encode only these tiles, emit tile-parts alone (0 = all, whole codestream)
+    bool tile_in_range(int t) const { return tile_count == 0 || ((uint32_t)t >= tile_first && (uint32_t)t < tile_first + tile_count); }
     bool tp_on = false;        // tile parts split by component (cinema)
     int tp_flag = 0;
     std::string comment;

@@ -83,6 +83,10 @@ void setup_coding_params(const ::j2kcuda_params& p, CodingParams& cp) {
         cp.tdx = cp.x1 - cp.tx0; cp.tdy = cp.y1 - cp.ty0;
         cp.tw = cp.th = 1;
     }
+    cp.tile_first = p.tile_count ? p.tile_first : 0;
+    cp.tile_count = p.tile_count;
+    if (cp.tile_count && cp.tile_first + cp.tile_count > cp.tw * cp.th)
+        cp.tile_count = cp.tile_first < cp.tw * cp.th ? cp.tw * cp.th - cp.tile_first : 0, cp.tile_first = cp.tile_count ? cp.tile_first : 0;
     cp.numlayers = numlayers;
     for (int i = 0; i < 16; ++i) cp.rates[i] = i < numlayers ? rates[i] : 0;
     cp.csty = csty;
@@ -453,7 +457,14 @@ bool EncoderHost::assemble(std::vector<EncTile>& tiles, std::vector<uint8_t>& ou
     if ((int)tiles.size() != nt) { err = "tile count mismatch"; return false; }
     std::vector<std::vector<TilePart>> parts(nt);
     int total_tp = 0;
-    for (int i = 0; i < nt; ++i) { tile_parts(cp, tiles[i].geo, parts[i]); total_tp += (int)parts[i].size(); }
+    const bool fragment = cp.tile_count != 0;
+    for (int i = 0; i < nt; ++i) {
+        if (!cp.tile_in_range(i) && fragment) {
+            // tile-part counts of the other ranks' tiles are still needed for the header's size
+            TileGeo g; build_tile(cp, i, 1.0f, g); tile_parts(cp, g, parts[i]);
+        } else tile_parts(cp, tiles[i].geo, parts[i]);
+        total_tp += (int)parts[i].size();
+    }
     size_t tlm_pos = 0;
     out.clear();
     {
@@ -463,14 +474,18 @@ bool EncoderHost::assemble(std::vector<EncTile>& tiles, std::vector<uint8_t>& ou
             for (auto& b : t.blocks) if (b.totalpasses > 0) est += (size_t)b.rates[b.totalpasses - 1] + 8;
             est += t.blocks.size() * 4 + 4096;
         }
+        (void)fragment;
         out.reserve(est);
     }
     write_main_header(cp, total_tp, out, tlm_pos);
     const bool cinema = tlm_pos != 0;
+    if (cinema && fragment) { err = "tile ranges cannot be combined with the cinema profiles (TLM)"; return false; }
+    const size_t header_len = out.size();
     // j2k.cpp:4355-4449: layer rates (compression ratios) -> byte budgets per tile
     const double sot_remove = (double)out.size() / nt;
     std::vector<uint8_t> tlm;
     for (int i = 0; i < nt; ++i) {
+        if (!cp.tile_in_range(i)) continue;
         EncTile& t = tiles[i];
         double rates[16];
         double offset = (cp.tp_on ? (double)(float)((parts[i].size() - 1) * 14) : 0.0) / cp.numlayers;
@@ -530,8 +545,54 @@ bool EncoderHost::assemble(std::vector<EncTile>& tiles, std::vector<uint8_t>& ou
         }
     }
     if (getenv("J2KCUDA_T2_TIMING")) fprintf(stderr, "assemble total %.2f ms\n", std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - tS).count());
+    if (fragment) { out.erase(out.begin(), out.begin() + (long)header_len); return true; }   // tile-parts alone
     put(out, 0xffd9, 2);                                                           // EOC
     if (cinema) std::copy(tlm.begin(), tlm.end(), out.begin() + (long)tlm_pos);
+    return true;
+}
+
+// One frame from the tile-part fragments of several encoders (tile ranges): main header, the
+// fragments ordered by the tile index of their first SOT, EOC.
+bool join_tile_streams(const CodingParams& cp_in, const uint8_t* const* frags, const size_t* lens, int nfrags,
+                       std::vector<uint8_t>& out, std::string& err) {
+    CodingParams cp = cp_in;
+    cp.tile_first = cp.tile_count = 0;
+    const int nt = (int)(cp.tw * cp.th);
+    int total_tp = 0;
+    for (int i = 0; i < nt; ++i) {
+        TileGeo g; std::vector<TilePart> parts;
+        build_tile(cp, i, 1.0f, g); tile_parts(cp, g, parts);
+        total_tp += (int)parts.size();
+    }
+    size_t tlm_pos = 0;
+    out.clear();
+    size_t total = 65536;
+    for (int i = 0; i < nfrags; ++i) total += lens[i];
+    out.reserve(total);
+    write_main_header(cp, total_tp, out, tlm_pos);
+    if (tlm_pos) { err = "cinema profiles (TLM) cannot be joined from tile fragments"; return false; }
+    std::vector<std::pair<int, int>> order;          // (first tile index, fragment)
+    std::vector<char> seen((size_t)nt, 0);
+    for (int i = 0; i < nfrags; ++i) {
+        if (lens[i] == 0) continue;
+        // walk the tile-parts of the fragment: SOT (0xff90), Lsot = 10, Isot, Psot
+        size_t pos = 0; int first = -1;
+        while (pos < lens[i]) {
+            const uint8_t* q = frags[i] + pos;
+            if (lens[i] - pos < 12 || q[0] != 0xff || q[1] != 0x90) { err = "fragment does not start at a tile-part"; return false; }
+            const int isot = (q[4] << 8) | q[5];
+            const size_t psot = ((size_t)q[6] << 24) | ((size_t)q[7] << 16) | ((size_t)q[8] << 8) | q[9];
+            if (isot >= nt || psot < 14 || psot > lens[i] - pos) { err = "bad tile-part in fragment"; return false; }
+            if (q[10] == 0) { if (seen[(size_t)isot]) { err = "tile present in two fragments"; return false; } seen[(size_t)isot] = 1; }
+            if (first < 0) first = isot;
+            pos += psot;
+        }
+        order.push_back({first, i});
+    }
+    for (int t = 0; t < nt; ++t) if (!seen[(size_t)t]) { err = "tile " + std::to_string(t) + " is missing from the fragments"; return false; }
+    std::sort(order.begin(), order.end());
+    for (auto& o : order) out.insert(out.end(), frags[o.second], frags[o.second] + lens[o.second]);
+    put(out, 0xffd9, 2);
     return true;
 }
 
