@@ -636,10 +636,10 @@ k_dwt_inverse(const DwtJob* __restrict__ jobs) {
 
 // Tunables (overridable through the environment for sweeps): columns per lane, software prefetch,
 // and the number of warp work items a launch should at least offer the 148 SMs.
-struct DwtTune { int ncol, pf_fwd, pf_inv, min_items, owners, gran; };
+struct DwtTune { int ncol, pf_fwd, pf_inv, min_items, owners, gran, min_sp, floor_items; };
 static const DwtTune& tune() {
     static DwtTune t = [] {
-        DwtTune v{4, 1, 2, 148 * 96, 30, 1};
+        DwtTune v{4, 1, 2, 148 * 96, 30, 1, 8, 148 * 16};
         auto geti = [](const char* name, int dflt) { const char* s = getenv(name); return s ? atoi(s) : dflt; };
         v.ncol = geti("J2KCUDA_DWT_NCOL", v.ncol) == 8 ? 8 : 4;
         v.pf_fwd = geti("J2KCUDA_DWT_PF", v.pf_fwd);
@@ -650,6 +650,8 @@ static const DwtTune& tune() {
         if (v.min_items < 1) v.min_items = 1;
         v.owners = geti("J2KCUDA_DWT_OWNERS", v.owners);
         if (v.owners < 1 || v.owners > 30) v.owners = 30;
+        v.min_sp = geti("J2KCUDA_DWT_MINSP", v.min_sp);
+        v.floor_items = geti("J2KCUDA_DWT_FLOOR", v.floor_items);
         v.gran = geti("J2KCUDA_DWT_GRAN", v.gran);
         if (v.gran < 1 || v.gran > v.owners) v.gran = 1;
         return v;
@@ -690,7 +692,11 @@ static int pick_seg_pairs(const DwtJob* jobs, int njobs) {
             items += (long long)ns * ((pairs + sp - 1) / sp);
         }
         best = sp;
+        // preferred: enough items to hide the row-to-row dependency of every warp; below 8 row pairs per
+        // segment the warm-up rows (1 pair for 5/3, 3 for 9/7) cost more than the extra warps bring, so the
+        // small levels only go shorter while the launch would not even give every SM `floor_items` warps
         if (items >= t.min_items) break;
+        if (sp <= t.min_sp && items >= t.floor_items) break;
     }
     return (int)best;
 }
