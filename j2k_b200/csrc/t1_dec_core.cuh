@@ -191,13 +191,16 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
             // ---- which columns can hold anything to decode in this pass ----
             u64 memb[4], cols = 0, memall = 0;
             if (passtype == 0) {
-                // significance propagation: columns that have (or acquire, from the column just scanned)
-                // a significant sample in their 3x6 window
+                // significance propagation: only columns that hold a candidate (an insignificant sample with a
+                // significant neighbour) are visited; a sample that turns significant adds the next column
+                u64 Hd[6];
 #pragma unroll
-                for (int q = 0; q < 6; ++q) cols |= (S[q] << 1) | S[q] | (S[q] >> 1);
-                cols &= colmask;
+                for (int q = 0; q < 6; ++q) Hd[q] = (S[q] << 1) | S[q] | (S[q] >> 1);
 #pragma unroll
-                for (int r = 0; r < 4; ++r) memb[r] = ~S[r + 1] & valid[r];
+                for (int r = 0; r < 4; ++r) {
+                    memb[r] = ~S[r + 1] & valid[r];
+                    cols |= memb[r] & (Hd[r] | Hd[r + 2] | (S[r + 1] << 1) | (S[r + 1] >> 1));
+                }
             } else if (passtype == 1) {
 #pragma unroll
                 for (int r = 0; r < 4; ++r) { memb[r] = S[r + 1] & ~V[r] & valid[r]; cols |= memb[r]; }
