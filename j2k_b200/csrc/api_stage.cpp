@@ -149,7 +149,7 @@ int j2kcuda_stage_t1_encode(const int32_t* plane, int stride, int height, const 
         size_t ocap = (64 + area * 28 / 4 + 15) & ~(size_t)15;
         b.out_off = (uint32_t)out_off; b.out_cap = (uint32_t)ocap; out_off += ocap;
     }
-    CK(BL.alloc(sizeof(T1Block) * nblk)); CK(SYM.alloc(sym_units * 16)); CK(OUT.alloc(out_off));
+    CK(BL.alloc(sizeof(T1Block) * nblk)); CK(SYM.alloc(sym_units * 16 + 64)); CK(OUT.alloc(out_off));
     CK(PN.alloc((size_t)nblk * T1_MAX_PASSES * 4)); CK(RES.alloc((size_t)nblk * sizeof(T1Result)));
     CK(cudaMemcpy(BL.p, hb.data(), sizeof(T1Block) * nblk, cudaMemcpyHostToDevice));
     CK(cudaMemset(RES.p, 0, (size_t)nblk * sizeof(T1Result)));

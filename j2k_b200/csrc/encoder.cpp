@@ -187,7 +187,7 @@ static int setup_encoder(j2kcuda_encoder* e) {
     if (e->nblocks) {
         CK(cudaMalloc(&e->d_blocks, e->nblocks * sizeof(T1Block)));
         CK(cudaMemcpy(e->d_blocks, e->h_blocks.data(), e->nblocks * sizeof(T1Block), cudaMemcpyHostToDevice));
-        CK(cudaMalloc(&e->d_sym, e->sym_bytes));
+        CK(cudaMalloc(&e->d_sym, e->sym_bytes + 64));      // the MQ kernel reads one 8-byte word ahead
         CK(cudaMalloc(&e->d_out, e->out_bytes));
         CK(cudaMalloc(&e->d_packed, e->out_bytes));
         CK(cudaMalloc(&e->d_pass_nsym, (size_t)e->nblocks * T1_MAX_PASSES * sizeof(uint32_t)));

@@ -389,45 +389,56 @@ k_t1_context(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __
 // ---- MQ coder ----------------------------------------------------------------------------------
 constexpr int MQ_THREADS = 128;
 
+// Encoder registers of one code-block (mqc.cpp:91-103 keeps them in a struct in memory).  Branches
+// cost a warp whose lanes code different blocks the sum of both sides, so the byte output is
+// written without any: the carry goes into the pending byte unless that byte is 0xFF, and a pending
+// 0xFF makes the next byte a 7-bit one.
 struct MqEnc {
     uint32_t a, c, ct;
-    int nb;                   // index of the last byte produced (bp - start); -1 = none yet
-    uint32_t last;            // that byte, still in a register (a later carry may bump it)
+    int nb;                   // index of the pending byte (bp - start); -1 = none yet
+    uint32_t last;            // the pending byte, still in a register (a later carry may bump it)
     uint8_t* out;
-    int cap;
-    bool overflow;
-    __device__ __forceinline__ void advance(uint32_t byte) {
-        if (nb >= 0) { if (nb < cap) out[nb] = (uint8_t)last; else overflow = true; }
+    uint32_t cap;
+    uint32_t overflow;
+    __device__ __forceinline__ void byteout() {                // mqc.cpp:223-257
+        const uint32_t carry = last == 0xffu ? 0u : (c >> 27); // before the first byte: last = 0 and c < 2^27
+        last += carry;
+        c -= carry << 27;
+        const uint32_t seven = last == 0xffu ? 1u : 0u;
+        if ((uint32_t)nb < cap) out[nb] = (uint8_t)last;       // nb = -1 fails the unsigned test
+        else overflow |= (uint32_t)(nb >= 0);
         ++nb;
-        last = byte & 0xffu;
-    }
-    __device__ void byteout() {                                // mqc.cpp:223-257
-        if (nb < 0) { advance(c >> 19); c &= 0x7ffffu; ct = 8; }
-        else if (last == 0xffu) { advance(c >> 20); c &= 0xfffffu; ct = 7; }
-        else if ((c & 0x8000000u) == 0) { advance(c >> 19); c &= 0x7ffffu; ct = 8; }
-        else {
-            ++last;
-            if (last == 0xffu) { c &= 0x7ffffffu; advance(c >> 20); c &= 0xfffffu; ct = 7; }
-            else { advance(c >> 19); c &= 0x7ffffu; ct = 8; }
-        }
+        const uint32_t sh = 19u + seven;
+        last = c >> sh;
+        c &= (1u << sh) - 1u;
+        ct = 8u - seven;
     }
     __device__ __forceinline__ void renorm() {                 // mqc.cpp:259-269, shift count taken at once
         uint32_t n = __clz(a) - 16;
-        while (n) {
-            const uint32_t k = n < ct ? n : ct;
-            a <<= k; c <<= k; ct -= k; n -= k;
-            if (ct == 0) byteout();
+        a <<= n;
+        while (n >= ct) {
+            c <<= ct; n -= ct;
+            byteout();
         }
+        c <<= n; ct -= n;
     }
 };
 
+// One code-block per thread, `lanes` threads of a warp in use.  The kernel is bound by the dependent
+// chain of its longest block (a lone warp per scheduler at the end), so the decision step is written
+// without branches: every branch costs such a warp a pipeline bubble several times the arithmetic it
+// skips.  What is left on the loop-carried chain is  a -= qe -> compare -> select -> clz -> shift  and,
+// when one context repeats, one table look-up.  Context states are kept as the probability-table WORD of
+// the current state (qe | mps << 15 | next-if-MPS << 16 | next-if-LPS << 24); the word of the next
+// symbol's context is fetched before the current one is updated and patched when both are the same.
+// Only two rarely taken branches remain per decision: byte output and pass boundary.
 __global__ void __launch_bounds__(MQ_THREADS)
 k_t1_mq(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __restrict__ tab,
         const uint8_t* __restrict__ sym_arena, const uint32_t* __restrict__ pass_nsym,
         uint8_t* __restrict__ out_arena, T1Result* __restrict__ results, int lanes) {
     __shared__ uint32_t s_mq[96];
     __shared__ uint32_t s_ctx[32][MQ_THREADS];
-    if (threadIdx.x < 94) s_mq[threadIdx.x] = tab->mq[threadIdx.x];
+    if (threadIdx.x < 94) s_mq[threadIdx.x] = tab->mq[threadIdx.x] | ((threadIdx.x & 1u) << 15);
     __syncthreads();
     const int lane = threadIdx.x & 31;
     const int gwarp = blockIdx.x * (MQ_THREADS / 32) + (threadIdx.x >> 5);
@@ -439,59 +450,59 @@ k_t1_mq(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __restr
     const T1Block blk = blocks[bi];
     const int t = threadIdx.x;
 #pragma unroll
-    for (int k = 0; k < 32; ++k) s_ctx[k][t] = 0;
-    s_ctx[CTX_UNI][t] = 46 * 2; s_ctx[CTX_AGG][t] = 3 * 2; s_ctx[CTX_ZC][t] = 4 * 2;     // t1_opt.cpp:686-690
+    for (int k = 0; k < 32; ++k) s_ctx[k][t] = s_mq[0];
+    s_ctx[CTX_UNI][t] = s_mq[46 * 2]; s_ctx[CTX_AGG][t] = s_mq[3 * 2]; s_ctx[CTX_ZC][t] = s_mq[4 * 2];   // t1_opt.cpp:686-690
 
     MqEnc q;
     q.a = 0x8000u; q.c = 0; q.ct = 12; q.nb = -1; q.last = 0;                           // mqc.cpp:406-420
-    q.out = out_arena + blk.out_off; q.cap = (int)blk.out_cap; q.overflow = false;
-    // The symbol stream is read 16 bytes at a time, one chunk ahead of its use, and the context-state
-    // and probability-table look-ups of symbol i+1 are issued before symbol i is coded, so that the
-    // loop-carried chain is only the interval update itself.
-    const uint4* sp = reinterpret_cast<const uint4*>(sym_arena + (size_t)blk.sym_off * 16);
+    q.out = out_arena + blk.out_off; q.cap = blk.out_cap; q.overflow = 0;
+    // The symbol stream ((ctx << 1) | d, one byte per decision) is read 8 bytes at a time, two words ahead
+    // (the arena is padded past the last symbol).
+    const u64* sp = reinterpret_cast<const u64*>(sym_arena + (size_t)blk.sym_off * 16);
     const uint32_t* pn = pass_nsym + (size_t)bi * T1_MAX_PASSES;
     const uint32_t nsym = res.nsym;
     int pass = 0;
-    uint32_t pend = pn[0], pos = 0;
-    uint4 nxt = nsym ? __ldg(sp) : make_uint4(0, 0, 0, 0);
-    uint32_t cctx = (nxt.x & 0xffu) >> 1;
-    uint32_t cst = s_ctx[cctx & 31u][t], ce = s_mq[cst];
-    for (uint32_t base = 0; base < nsym; base += 16) {
-        const uint4 cur = nxt;
-        if (base + 16 < nsym) nxt = __ldg(sp + (base >> 4) + 1);
-        const uint32_t w[5] = {cur.x, cur.y, cur.z, cur.w, nxt.x};
+    uint32_t pend = pn[0];
+    u64 cur = __ldg(sp), nxt = __ldg(sp + 1);
+    uint32_t sym = (uint32_t)cur & 0xffu, ctx = (sym >> 1) & 31u;
+    uint32_t e = s_ctx[ctx][t];
+    for (uint32_t base = 0; base < nsym; base += 8) {
+        const u64 w0 = cur, w1 = nxt;
+        cur = nxt;
+        nxt = __ldg(sp + (base >> 3) + 2);
 #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            if (base + k >= nsym) break;
-            while (pass < npasses && pos == pend) {            // t1_opt.cpp:719
-                res.rate[pass] = (q.nb < 0 ? 0 : q.nb) + 3;
-                if (++pass < npasses) pend += pn[pass];
+        for (int k = 0; k < 8; ++k) {
+            const uint32_t pos = base + k;
+            if (pos >= nsym) break;
+            if (pos == pend) {                                  // t1_opt.cpp:719
+                do {
+                    res.rate[pass] = (q.nb < 0 ? 0 : q.nb) + 3;
+                    if (++pass < npasses) pend += pn[pass];
+                } while (pass < npasses && pos == pend);
             }
-            const uint32_t d = (w[k >> 2] >> ((k & 3) * 8)) & 1u;
-            const uint32_t ns = (w[(k + 1) >> 2] >> (((k + 1) & 3) * 8)) & 0xffu;
-            const uint32_t nctx = (ns >> 1) & 31u;
-            uint32_t nst = s_ctx[nctx][t];
-            uint32_t ne = s_mq[nst];
-            const uint32_t qe = ce & 0xffffu;
-            q.a -= qe;
-            uint32_t newst = cst;
-            if (d == (cst & 1u)) {                             // MPS, mqc.cpp:271-285
-                if (q.a & 0x8000u) { q.c += qe; }
-                else {
-                    if (q.a < qe) q.a = qe; else q.c += qe;
-                    newst = (ce >> 16) & 0xffu;
-                }
-            } else {                                           // LPS, mqc.cpp:287-297
-                if (q.a < qe) q.c += qe; else q.a = qe;
-                newst = ce >> 24;
+            // the next decision's context word, fetched before this one's update
+            const uint32_t nsymb = k < 7 ? (uint32_t)(w0 >> (8 * (k + 1))) & 0xffu : (uint32_t)w1 & 0xffu;
+            const uint32_t nctx = (nsymb >> 1) & 31u;
+            uint32_t ne = s_ctx[nctx][t];
+            // mqc.cpp:271-297 without branches
+            const uint32_t qe = e & 0x7fffu;
+            const uint32_t lps = (sym ^ (e >> 15)) & 1u;
+            uint32_t a = q.a - qe;
+            const bool lt = a < qe;
+            const bool ren = lps || !(a & 0x8000u);             // every path that renormalises also moves the state
+            const bool xch = (lps != 0) != lt;                  // interval becomes qe: MPS with a < qe, LPS with a >= qe
+            const uint32_t newe = s_mq[lps ? (e >> 24) : ((e >> 16) & 0xffu)];
+            a = xch ? qe : a;
+            q.c += xch ? 0u : qe;
+            if (ren) s_ctx[ctx][t] = newe;
+            if (ren && nctx == ctx) ne = newe;
+            uint32_t n = __clz(a) - 16;                         // mqc.cpp:259-269, shift count taken at once
+            q.a = a << n;
+            if (n >= q.ct) {
+                do { q.c <<= q.ct; n -= q.ct; q.byteout(); } while (n >= q.ct);
             }
-            if (!(q.a & 0x8000u)) {                            // every path that changes the state renormalises
-                s_ctx[cctx][t] = newst;
-                if (nctx == cctx) { nst = newst; ne = s_mq[newst]; }
-                q.renorm();
-            }
-            cctx = nctx; cst = nst; ce = ne;
-            ++pos;
+            q.c <<= n; q.ct -= n;
+            sym = nsymb; ctx = nctx; e = ne;
         }
     }
     while (pass < npasses) {
@@ -506,7 +517,7 @@ k_t1_mq(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __restr
         q.c <<= q.ct; q.byteout();
         q.c <<= q.ct; q.byteout();
     }
-    if (q.nb >= 0) { if (q.nb < q.cap) q.out[q.nb] = (uint8_t)q.last; else q.overflow = true; }
+    if (q.nb >= 0) { if ((uint32_t)q.nb < q.cap) q.out[q.nb] = (uint8_t)q.last; else q.overflow = 1; }
     int total = q.nb < 0 ? 0 : q.nb;
     if (q.last != 0xffu) ++total;
     if (q.overflow) { res.status = 2; res.total = 0; return; }
