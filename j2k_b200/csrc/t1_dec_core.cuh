@@ -37,7 +37,7 @@ struct DRows {                // index = row + 1
 // (which reproduces the reference's behaviour at and past the end of the data, mqc.cpp:336-365) and
 // by at least 24 more readable bytes.
 struct MqDec {
-    uint32_t a, c, ct;
+    uint32_t a, c, ct;        // a is kept shifted left by 16 so that it lines up with the code bits of c
     const u64* wp;            // next word to fetch
     u64 w0, w1;               // bytes [8k, 8k+8) and [8k+8, 8k+16) of the segment
     uint32_t off;             // position of the current byte inside w0
@@ -58,33 +58,36 @@ struct MqDec {
         off = 0;
         c = ((uint32_t)w0 & 0xffu) << 16;
         bytein();
-        c <<= 7; ct -= 7; a = 0x8000u;
+        c <<= 7; ct -= 7; a = 0x80000000u;
     }
-    J2K_HD inline void renorm() {                         // a < 0x8000: shift until bit 15 is set, refilling c
-        uint32_t n = (uint32_t)J2K_CLZ(a) - 16u;
-        do {
-            if (ct == 0) bytein();
-            const uint32_t k = n < ct ? n : ct;
-            a <<= k; c <<= k; ct -= k; n -= k;
-        } while (n);
+    J2K_HD inline void renorm() {                         // a < 0x8000: shift until the top bit is set, refilling c
+        uint32_t n = (uint32_t)J2K_CLZ(a);                // (bytes are fetched only when a shift needs them, mqc.cpp:367-378)
+        a <<= n;
+        if (n > ct) {
+            do {
+                c <<= ct; n -= ct;
+                bytein();
+            } while (n > ct);
+        }
+        c <<= n; ct -= n;
     }
-    // st: per-context state WORD = the probability-table entry of the context's current state with the
-    // MPS in bit 15 (Qe uses 15 bits): qe | mps << 15 | next-if-MPS << 16 | next-if-LPS << 24; tab = that
-    // table (mq_state_words).  One shared-memory look-up per decision, a second only when the state moves.
+    // st: per-context state WORD = the probability-table entry of the context's current state:
+    //   qe << 16 | next-if-LPS << 8 | next-if-MPS << 1 | mps   (next-* index the table, tab = mq_state_words).
+    // One shared-memory look-up per decision, a second only when the state moves.
     J2K_HD inline uint32_t decode(uint32_t* st, const uint32_t* tab, uint32_t ctx) {   // mqc.cpp:577-595
-        const uint32_t e = st[ctx], qe = e & 0x7fffu;
-        uint32_t d = (e >> 15) & 1u;
+        const uint32_t e = st[ctx], qe = e & 0xffff0000u;
+        uint32_t d = e & 1u;
         a -= qe;
-        if ((c >> 16) < qe) {
-            if (a < qe) st[ctx] = tab[(e >> 16) & 0xffu];
-            else { d ^= 1u; st[ctx] = tab[e >> 24]; }
+        if (c < qe) {
+            if (a < qe) st[ctx] = tab[(e >> 1) & 0x7fu];
+            else { d ^= 1u; st[ctx] = tab[(e >> 8) & 0x7fu]; }
             a = qe;
             renorm();
         } else {
-            c -= qe << 16;
-            if ((a & 0x8000u) == 0) {
-                if (a < qe) { d ^= 1u; st[ctx] = tab[e >> 24]; }
-                else st[ctx] = tab[(e >> 16) & 0xffu];
+            c -= qe;
+            if ((int32_t)a >= 0) {
+                if (a < qe) { d ^= 1u; st[ctx] = tab[(e >> 8) & 0x7fu]; }
+                else st[ctx] = tab[(e >> 1) & 0x7fu];
                 renorm();
             }
         }
@@ -92,8 +95,11 @@ struct MqDec {
     }
 };
 
-// state word table from T1Tables::mq (entry s = state index * 2 + mps)
-J2K_HD inline uint32_t mq_state_word(const uint32_t* mq, int s) { return mq[s] | ((uint32_t)(s & 1) << 15); }
+// state word table from T1Tables::mq (entry s = state index * 2 + mps: qe | next-if-MPS << 16 | next-if-LPS << 24)
+J2K_HD inline uint32_t mq_state_word(const uint32_t* mq, int s) {
+    const uint32_t m = mq[s];
+    return ((m & 0xffffu) << 16) | ((m >> 24) << 8) | (((m >> 16) & 0x7fu) << 1) | (uint32_t)(s & 1);
+}
 
 J2K_HD inline uint32_t w3(u64 m, int x) {          // bits x-1, x, x+1 of a row
     return (uint32_t)(x ? (m >> (x - 1)) : (m << 1)) & 7u;

@@ -466,45 +466,53 @@ k_t1_mq(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __restr
     u64 cur = __ldg(sp), nxt = __ldg(sp + 1);
     uint32_t sym = (uint32_t)cur & 0xffu, ctx = (sym >> 1) & 31u;
     uint32_t e = s_ctx[ctx][t];
+    // one decision, mqc.cpp:271-297 without branches; nsymb = the next decision's symbol byte
+#define J2K_MQ_STEP(nsymb_expr)                                                                        \
+    {                                                                                                  \
+        const uint32_t nsymb = (nsymb_expr);                                                           \
+        const uint32_t nctx = (nsymb >> 1) & 31u;                                                      \
+        uint32_t ne = s_ctx[nctx][t];              /* fetched before this decision's update */          \
+        const uint32_t qe = e & 0x7fffu;                                                               \
+        const uint32_t lps = (sym ^ (e >> 15)) & 1u;                                                   \
+        uint32_t a = q.a - qe;                                                                         \
+        const bool lt = a < qe;                                                                        \
+        const bool ren = lps || !(a & 0x8000u);    /* every path that renormalises also moves the state */ \
+        const bool xch = (lps != 0) != lt;         /* interval becomes qe: MPS with a < qe, LPS with a >= qe */ \
+        const uint32_t newe = s_mq[lps ? (e >> 24) : ((e >> 16) & 0xffu)];                             \
+        a = xch ? qe : a;                                                                              \
+        q.c += xch ? 0u : qe;                                                                          \
+        if (ren) s_ctx[ctx][t] = newe;                                                                 \
+        if (ren && nctx == ctx) ne = newe;                                                             \
+        uint32_t n = __clz(a) - 16;                /* mqc.cpp:259-269, shift count taken at once */      \
+        q.a = a << n;                                                                                  \
+        if (n >= q.ct) {                                                                               \
+            do { q.c <<= q.ct; n -= q.ct; q.byteout(); } while (n >= q.ct);                            \
+        }                                                                                              \
+        q.c <<= n; q.ct -= n;                                                                          \
+        sym = nsymb; ctx = nctx; e = ne;                                                               \
+    }
     for (uint32_t base = 0; base < nsym; base += 8) {
         const u64 w0 = cur, w1 = nxt;
         cur = nxt;
         nxt = __ldg(sp + (base >> 3) + 2);
+        if (base + 8 <= nsym && pend - base >= 8) {
+            // whole word inside one pass: no per-decision bookkeeping
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const uint32_t pos = base + k;
-            if (pos >= nsym) break;
-            if (pos == pend) {                                  // t1_opt.cpp:719
-                do {
+            for (int k = 0; k < 8; ++k) J2K_MQ_STEP(k < 7 ? (uint32_t)(w0 >> (8 * (k + 1))) & 0xffu : (uint32_t)w1 & 0xffu)
+        } else {
+#pragma unroll 1
+            for (int k = 0; k < 8; ++k) {
+                const uint32_t pos = base + k;
+                if (pos >= nsym) break;
+                while (pass < npasses && pos == pend) {         // t1_opt.cpp:719
                     res.rate[pass] = (q.nb < 0 ? 0 : q.nb) + 3;
                     if (++pass < npasses) pend += pn[pass];
-                } while (pass < npasses && pos == pend);
+                }
+                J2K_MQ_STEP(k < 7 ? (uint32_t)(w0 >> (8 * (k + 1))) & 0xffu : (uint32_t)w1 & 0xffu)
             }
-            // the next decision's context word, fetched before this one's update
-            const uint32_t nsymb = k < 7 ? (uint32_t)(w0 >> (8 * (k + 1))) & 0xffu : (uint32_t)w1 & 0xffu;
-            const uint32_t nctx = (nsymb >> 1) & 31u;
-            uint32_t ne = s_ctx[nctx][t];
-            // mqc.cpp:271-297 without branches
-            const uint32_t qe = e & 0x7fffu;
-            const uint32_t lps = (sym ^ (e >> 15)) & 1u;
-            uint32_t a = q.a - qe;
-            const bool lt = a < qe;
-            const bool ren = lps || !(a & 0x8000u);             // every path that renormalises also moves the state
-            const bool xch = (lps != 0) != lt;                  // interval becomes qe: MPS with a < qe, LPS with a >= qe
-            const uint32_t newe = s_mq[lps ? (e >> 24) : ((e >> 16) & 0xffu)];
-            a = xch ? qe : a;
-            q.c += xch ? 0u : qe;
-            if (ren) s_ctx[ctx][t] = newe;
-            if (ren && nctx == ctx) ne = newe;
-            uint32_t n = __clz(a) - 16;                         // mqc.cpp:259-269, shift count taken at once
-            q.a = a << n;
-            if (n >= q.ct) {
-                do { q.c <<= q.ct; n -= q.ct; q.byteout(); } while (n >= q.ct);
-            }
-            q.c <<= n; q.ct -= n;
-            sym = nsymb; ctx = nctx; e = ne;
         }
     }
+#undef J2K_MQ_STEP
     while (pass < npasses) {
         res.rate[pass] = (q.nb < 0 ? 0 : q.nb) + 3;
         ++pass;
