@@ -155,7 +155,7 @@ int j2kcuda_stage_t1_encode(const int32_t* plane, int stride, int height, const 
     CK(cudaMemset(RES.p, 0, (size_t)nblk * sizeof(T1Result)));
     launch_t1_context(BL.as<T1Block>(), nblk, SYM.as<uint8_t>(), PN.as<uint32_t>(), RES.as<T1Result>(), 0);
     CK(cudaDeviceSynchronize());
-    launch_t1_mq(BL.as<T1Block>(), nblk, SYM.as<uint8_t>(), PN.as<uint32_t>(), OUT.as<uint8_t>(), RES.as<T1Result>(), 32, 0);
+    launch_t1_mq(BL.as<T1Block>(), nblk, SYM.as<uint8_t>(), PN.as<uint32_t>(), OUT.as<uint8_t>(), RES.as<T1Result>(), 32, nullptr, 0, 0);
     CK(cudaDeviceSynchronize());
     std::vector<T1Result> hr(nblk);
     std::vector<uint8_t> ho(out_off);

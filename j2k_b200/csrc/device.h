@@ -97,7 +97,9 @@ void launch_t1_context(const T1Block* d_blocks, int nblocks, uint8_t* sym_arena,
                        T1Result* results, cudaStream_t st);
 void launch_t1_mq(const T1Block* d_blocks, int nblocks, const uint8_t* sym_arena,
                   const uint32_t* pass_nsym, uint8_t* out_arena, T1Result* results,
-                  int lanes_per_warp, cudaStream_t st);
+                  int lanes_per_warp, uint32_t* d_order, int max_long, cudaStream_t st);
+// (d_order: scratch of nblocks + 2 words, or null: filled with the block indices by decreasing symbol count;
+//  the blocks at least half as long as the longest, at most max_long of them, get a warp each)
 // gather the kept bytes of every block into one contiguous buffer (offsets = exclusive scan of
 // T1Result::total, written to d_offsets[nblocks+1])
 void launch_t1_compact(const T1Block* d_blocks, int nblocks, const uint8_t* out_arena,

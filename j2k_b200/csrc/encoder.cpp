@@ -56,7 +56,8 @@ struct j2kcuda_encoder {
     uint32_t* h_offsets = nullptr;                   // pinned
     uint8_t* h_packed = nullptr; size_t h_packed_cap = 0;   // pinned
     std::vector<std::vector<double>> dist;           // per block cumulative distortion
-    int mq_lanes = 32;
+    int mq_lanes = 4;
+    uint32_t* d_mq_order = nullptr; int mq_nlong = 592;  // MQ kernel: blocks by decreasing symbol count, at most mq_nlong of the longest get a warp each
     int row0 = 0, row1 = 0;    // image rows covered by this context's tiles (all rows unless a tile range is set)
     // timing
     cudaEvent_t ev[10];
@@ -70,7 +71,7 @@ static void free_encoder(j2kcuda_encoder* e) {
     cudaSetDevice(e->device);
     for (int c = 0; c < 4; ++c) { cudaFree(e->planeA[c]); cudaFree(e->planeB[c]); }
     cudaFree(e->d_pix); cudaFreeHost(e->h_pix);
-    cudaFree(e->d_jobs); cudaFree(e->d_blocks); cudaFree(e->d_sym); cudaFree(e->d_out);
+    cudaFree(e->d_mq_order); cudaFree(e->d_jobs); cudaFree(e->d_blocks); cudaFree(e->d_sym); cudaFree(e->d_out);
     cudaFree(e->d_pass_nsym); cudaFree(e->d_results); cudaFree(e->d_offsets); cudaFree(e->d_packed);
     cudaFreeHost(e->h_results); cudaFreeHost(e->h_offsets); cudaFreeHost(e->h_packed);
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
@@ -193,11 +194,13 @@ static int setup_encoder(j2kcuda_encoder* e) {
         CK(cudaMalloc(&e->d_pass_nsym, (size_t)e->nblocks * T1_MAX_PASSES * sizeof(uint32_t)));
         CK(cudaMalloc(&e->d_results, (size_t)e->nblocks * sizeof(T1Result)));
         CK(cudaMalloc(&e->d_offsets, ((size_t)e->nblocks + 1) * sizeof(uint32_t)));
+        CK(cudaMalloc(&e->d_mq_order, ((size_t)e->nblocks + 2) * sizeof(uint32_t)));
         CK(cudaMallocHost(&e->h_results, (size_t)e->nblocks * sizeof(T1Result)));
         CK(cudaMallocHost(&e->h_offsets, ((size_t)e->nblocks + 1) * sizeof(uint32_t)));
     }
     e->dist.assign(e->nblocks, {});
     if (const char* s = getenv("J2KCUDA_MQ_LANES")) { int v = atoi(s); if (v >= 1 && v <= 32) e->mq_lanes = v; }
+    if (const char* s = getenv("J2KCUDA_MQ_NLONG")) e->mq_nlong = atoi(s);
     // sample conversion parameters
     memset(&e->mp, 0, sizeof(e->mp));
     e->mp.width = e->W; e->mp.height = e->H; e->mp.pitch = e->pitch; e->mp.ncomp = e->ncomp;
@@ -370,7 +373,7 @@ int j2kcuda_encoder_run(j2kcuda_encoder* e) {
     CK(cudaEventRecord(e->ev[2], st));
     launch_t1_context(e->d_blocks, e->nblocks, e->d_sym, e->d_pass_nsym, e->d_results, st); ++launches;
     CK(cudaEventRecord(e->ev[3], st));
-    launch_t1_mq(e->d_blocks, e->nblocks, e->d_sym, e->d_pass_nsym, e->d_out, e->d_results, e->mq_lanes, st); ++launches;
+    launch_t1_mq(e->d_blocks, e->nblocks, e->d_sym, e->d_pass_nsym, e->d_out, e->d_results, e->mq_lanes, e->d_mq_order, e->mq_nlong, st); launches += 2;
     CK(cudaEventRecord(e->ev[4], st));
     launch_t1_compact(e->d_blocks, e->nblocks, e->d_out, e->d_results, e->d_offsets, e->d_packed, st); launches += 2;
     if (e->nblocks) {

@@ -243,14 +243,19 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
                     uint32_t win = cb.win[x];
                     if (x == carry_x + 1) win |= carry_s;
                     const uint32_t mem4 = cb.aux[x];
+                    // rows of this column to code: insignificant with a significant neighbour.  Bit 3q of
+                    // rowany / side = any of row q's three window bits / its left or right one.
+                    const uint32_t rowany = (win | (win >> 1) | (win >> 2)) & 0x9249u;
+                    const uint32_t side = (win | (win >> 2)) & 0x9249u;
+                    const uint32_t nb = (rowany << 3) | (rowany >> 3) | side;       // bit 3(r + 1): sample r has a neighbour
+                    uint32_t todo = mem4 & (((nb >> 3) & 1u) | ((nb >> 5) & 2u) | ((nb >> 7) & 4u) | ((nb >> 9) & 8u));
                     uint32_t gwin = 0;
                     bool have_g = false;
-                    uint32_t new4 = 0, neg4 = 0, vis4 = 0;
-#pragma unroll 1
-                    for (int r = 0; r < 4; ++r) {
+                    uint32_t new4 = 0, neg4 = 0, vis4 = todo;
+                    while (todo) {
+                        const int r = J2K_FFSLL(todo) - 1;
+                        todo &= todo - 1;
                         const uint32_t s9 = (win >> (3 * r)) & 0x1ffu;
-                        if (!((mem4 >> r) & 1u) || !(s9 & 0x1efu)) continue;
-                        vis4 |= 1u << r;
                         if (!mq.decode(st, mqtab, zc[s9 & 0x1efu])) continue;
                         if (!have_g) {
                             u64 G[6];
@@ -265,6 +270,8 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
                         win |= 2u << (3 * r + 3);
                         gwin |= (neg << 1) << (3 * r + 3);
                         new4 |= 1u << r; neg4 |= neg << r;
+                        const uint32_t below = mem4 & (2u << r);                   // the row below now has a significant neighbour
+                        todo |= below; vis4 |= below;
                     }
                     if (vis4) { cb.out[x] = new4 | (neg4 << 4) | (vis4 << 8); any = true; }
                     if (new4) {
@@ -309,9 +316,10 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
                         partial = true;
                     }
                     uint32_t new4 = 0, neg4 = 0;
-#pragma unroll 1
-                    for (int r = rstart; r < 4; ++r) {
-                        if (!((mem4 >> r) & 1u)) continue;
+                    uint32_t todo = mem4 & (0xfu << rstart);
+                    while (todo) {
+                        const int r = J2K_FFSLL(todo) - 1;
+                        todo &= todo - 1;
                         const uint32_t s9 = (win >> (3 * r)) & 0x1ffu;
                         if (partial) partial = false;                  // the sample that ended the run is significant
                         else if (!mq.decode(st, mqtab, zc[s9 & 0x1efu])) continue;

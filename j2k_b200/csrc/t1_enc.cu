@@ -424,6 +424,42 @@ struct MqEnc {
     }
 };
 
+// Block indices by decreasing symbol count (512-symbol buckets); order[nblocks] = how many blocks are at least
+// half as long as the longest (at most max_long): those get a warp each in k_t1_mq; order[nblocks + 1] = blocks
+// per warp for the rest.  One CTA.
+__global__ void __launch_bounds__(1024) k_t1_order(const T1Result* __restrict__ results, int nblocks, int max_long, int lanes,
+                                                  uint32_t* __restrict__ order) {
+    __shared__ uint32_t s_hist[256], s_off[256];
+    __shared__ uint32_t s_max;
+    if (threadIdx.x < 256) s_hist[threadIdx.x] = 0;
+    if (threadIdx.x == 0) s_max = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < nblocks; i += blockDim.x) {
+        const uint32_t n = results[i].npasses > 0 ? results[i].nsym : 0u;
+        atomicAdd(&s_hist[min(n >> 9, 255u)], 1u);
+        atomicMax(&s_max, n);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t run = 0, nlong = 0;
+        const uint32_t half = min((s_max / 2) >> 9, 255u);
+        for (int b = 255; b >= 0; --b) {
+            s_off[b] = run; run += s_hist[b];
+            if ((uint32_t)b >= half && b > 0) nlong = run;
+        }
+        // many blocks about as long as the longest (noise-like content): the kernel is then bound by issue slots
+        // rather than by one chain, and full warps are the better shape
+        const bool flat = nlong * 4 > (uint32_t)nblocks;
+        order[nblocks] = flat ? 0u : min(nlong, (uint32_t)max(max_long, 0));
+        order[nblocks + 1] = flat ? 32u : (uint32_t)lanes;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < nblocks; i += blockDim.x) {
+        const uint32_t n = results[i].npasses > 0 ? results[i].nsym : 0u;
+        order[atomicAdd(&s_off[min(n >> 9, 255u)], 1u)] = (uint32_t)i;
+    }
+}
+
 // One code-block per thread, `lanes` threads of a warp in use.  The kernel is bound by the dependent
 // chain of its longest block (a lone warp per scheduler at the end), so the decision step is written
 // without branches: every branch costs such a warp a pipeline bubble several times the arithmetic it
@@ -435,15 +471,23 @@ struct MqEnc {
 __global__ void __launch_bounds__(MQ_THREADS)
 k_t1_mq(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __restrict__ tab,
         const uint8_t* __restrict__ sym_arena, const uint32_t* __restrict__ pass_nsym,
-        uint8_t* __restrict__ out_arena, T1Result* __restrict__ results, int lanes) {
+        uint8_t* __restrict__ out_arena, T1Result* __restrict__ results, int lanes,
+        const uint32_t* __restrict__ order) {
     __shared__ uint32_t s_mq[96];
     __shared__ uint32_t s_ctx[32][MQ_THREADS];
     if (threadIdx.x < 94) s_mq[threadIdx.x] = tab->mq[threadIdx.x] | ((threadIdx.x & 1u) << 15);
     __syncthreads();
     const int lane = threadIdx.x & 31;
     const int gwarp = blockIdx.x * (MQ_THREADS / 32) + (threadIdx.x >> 5);
-    const int bi = gwarp * lanes + lane;
-    if (lane >= lanes || bi >= nblocks) return;
+    // slots [0, nlong): one block per warp (the longest blocks, whose chain bounds the kernel: no lane of
+    // another block to wait for); the rest: `lanes` blocks per warp.  order[] = blocks by decreasing work.
+    const int nlong = order ? (int)order[nblocks] : 0;
+    if (order) lanes = (int)order[nblocks + 1];
+    int slot;
+    if (gwarp < nlong) { if (lane) return; slot = gwarp; }
+    else { if (lane >= lanes) return; slot = nlong + (gwarp - nlong) * lanes + lane; }
+    if (slot >= nblocks) return;
+    const int bi = order ? (int)order[slot] : slot;
     T1Result& res = results[bi];
     const int npasses = res.npasses;
     if (npasses == 0 || res.status != 0) { res.total = 0; return; }
@@ -591,13 +635,18 @@ void launch_t1_context(const T1Block* d_blocks, int nblocks, uint8_t* sym_arena,
 }
 
 void launch_t1_mq(const T1Block* d_blocks, int nblocks, const uint8_t* sym_arena, const uint32_t* pass_nsym,
-                  uint8_t* out_arena, T1Result* results, int lanes_per_warp, cudaStream_t st) {
+                  uint8_t* out_arena, T1Result* results, int lanes_per_warp, uint32_t* d_order, int max_long, cudaStream_t st) {
     if (nblocks <= 0) return;
     if (lanes_per_warp < 1) lanes_per_warp = 1;
     if (lanes_per_warp > 32) lanes_per_warp = 32;
-    const int warps = (nblocks + lanes_per_warp - 1) / lanes_per_warp;
+    if (max_long < 0 || !d_order) max_long = 0;
+    if (max_long > nblocks) max_long = nblocks;
+    if (d_order) k_t1_order<<<1, 1024, 0, st>>>(results, nblocks, max_long, lanes_per_warp, d_order);
+    // the grid covers the worst case (max_long single-block warps); warps past the real count exit at once
+    const int warps = max_long + (nblocks + lanes_per_warp - 1) / lanes_per_warp;
     const int wpc = MQ_THREADS / 32;
-    k_t1_mq<<<(warps + wpc - 1) / wpc, MQ_THREADS, 0, st>>>(d_blocks, nblocks, t1_tables_device(), sym_arena, pass_nsym, out_arena, results, lanes_per_warp);
+    k_t1_mq<<<(warps + wpc - 1) / wpc, MQ_THREADS, 0, st>>>(d_blocks, nblocks, t1_tables_device(), sym_arena, pass_nsym, out_arena, results,
+                                                         lanes_per_warp, d_order);
 }
 
 void launch_t1_compact(const T1Block* d_blocks, int nblocks, const uint8_t* out_arena, const T1Result* results,
