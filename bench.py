@@ -33,7 +33,7 @@ FRAMES = 16  # frames per step per GPU (one batch of the image sequence): 16 x 7
              # planes per frame in flight -- far beyond the 126 MB L2, so no flush is needed between steps
 TRAFFIC_L1 = 239528448  # dram__bytes_read.sum 142 346 240 + dram__bytes_write.sum 97 182 208 of one level-1 launch, from the
                         # ncu --set full capture in profiles/r1_roundtrip_full_raw.csv (part of the 141.6 MB written stays in L2)
-WORKERS = 8  # contexts (stream + buffers + host thread) the sequence keeps in flight
+WORKERS = 16  # contexts (stream + buffers + host thread) the sequence keeps in flight
 
 
 def peaks():

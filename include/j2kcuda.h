@@ -197,6 +197,55 @@ int j2kcuda_decode_batch(const uint8_t* const* streams, const size_t* lens, int 
 int j2kcuda_join_tile_streams(const j2kcuda_params* p, const uint8_t* const* frags, const size_t* lens,
                               int nfrags, uint8_t** out, size_t* out_len);
 
+/* ---- JP2 file wrapper (host only; ext/grok/src/lib/openjp2/jp2.cpp) ------------------------- */
+/* What OpenJPEGCodec::GetFileInfo takes from the JP2 header boxes through opj_read_header_ex
+ * (j2k_openjpeg_codec.cpp:303-408): enumerated colour space or ICC profile, channel definitions,
+ * palette + component mapping, resolution.  Replaces opj_jp2_read_header_procedure / read_ihdr /
+ * read_bpcc / read_colr / read_cdef / read_pclr / read_cmap / read_res (jp2.cpp:560-1816, 2383-2500). */
+#define J2KCUDA_JP2_MAX_CHANNELS 16
+typedef struct j2kcuda_jp2_info {
+    uint32_t is_jp2;                     /* 0: raw codestream, nothing else is set */
+    uint32_t brand, minversion;          /* ftyp: 'jp2 ' = 0x6a703220, 'jpx ' = 0x6a707820 */
+    uint32_t width, height, ncomp;       /* ihdr */
+    uint32_t bpc;                        /* ihdr: (depth - 1) | sign << 7; 255 = per component, see bpcc */
+    uint32_t unk_c, ipr;
+    uint32_t bpcc[J2KCUDA_JP2_MAX_CHANNELS];   /* (depth - 1) | sign << 7 per component (from bpcc, else bpc) */
+    uint32_t colr_method;                /* 0 no colr box, 1 enumerated, 2 restricted ICC, 3 any ICC, 4 vendor */
+    uint32_t enumcs;                     /* 12 CMYK, 16 sRGB, 17 grey, 18 sYCC, 19 esYCC ... */
+    uint32_t precedence, approx;
+    uint64_t icc_offset, icc_length;     /* ICC profile bytes inside the probed buffer */
+    uint32_t cdef_n;                     /* channel definitions: component cn has type typ (0 colour, 1 opacity, */
+    uint16_t cdef_cn[J2KCUDA_JP2_MAX_CHANNELS];     /* 2 premultiplied opacity, 65535 unspecified) and is */
+    uint16_t cdef_typ[J2KCUDA_JP2_MAX_CHANNELS];    /* associated with colour asoc (0 whole image, 1..n)  */
+    uint16_t cdef_asoc[J2KCUDA_JP2_MAX_CHANNELS];
+    uint32_t pclr_entries, pclr_channels;            /* palette: entries x channels */
+    uint8_t  pclr_depth[J2KCUDA_JP2_MAX_CHANNELS];   /* (depth - 1) | sign << 7 per palette column */
+    uint64_t pclr_offset;                /* first entry inside the probed buffer (big-endian, ceil(depth / 8) bytes each) */
+    uint32_t cmap_n;                     /* component mapping: output channel i = component cmp, direct (mtyp 0) */
+    uint16_t cmap_cmp[J2KCUDA_JP2_MAX_CHANNELS];    /* or through palette column pcol (mtyp 1) */
+    uint8_t  cmap_mtyp[J2KCUDA_JP2_MAX_CHANNELS], cmap_pcol[J2KCUDA_JP2_MAX_CHANNELS];
+    uint32_t has_capture_res, has_display_res;
+    double   capture_res[2], display_res[2];         /* vertical, horizontal, grid points per metre */
+    uint64_t codestream_offset, codestream_length;   /* contents of the jp2c box */
+} j2kcuda_jp2_info;
+int j2kcuda_probe_jp2(const uint8_t* bytes, size_t n, j2kcuda_jp2_info* out);
+/* palette entries as uint32 [entry][channel] (what opj_jp2_pclr_t::entries holds, jp2.cpp:1317-1419);
+ * returns the number of values written (entries x channels) or a negative error */
+int j2kcuda_jp2_palette(const uint8_t* bytes, size_t n, uint32_t* entries, size_t cap);
+
+/* Wrap a codestream into a JP2 file: jp, ftyp, jp2h{ihdr, [bpcc], colr, [cdef]}, jp2c -- the boxes
+ * and defaults of opj_jp2_setup_encoder + opj_jp2_write_* (jp2.cpp:646-1110, 1817-2060, 2058-2262);
+ * byte-identical to what the reference writes around the same codestream. */
+typedef struct j2kcuda_jp2_params {
+    uint32_t width, height, ncomp;
+    uint32_t prec[J2KCUDA_JP2_MAX_CHANNELS], sgnd[J2KCUDA_JP2_MAX_CHANNELS];
+    uint32_t enumcs;                     /* used when icc == NULL: 16 sRGB, 17 grey, 18 sYCC */
+    const uint8_t* icc; size_t icc_len;  /* restricted ICC profile -> colr method 2 */
+    int32_t  alpha_comp;                 /* component holding opacity (-> cdef box), -1 = none */
+} j2kcuda_jp2_params;
+int j2kcuda_wrap_jp2(const uint8_t* codestream, size_t len, const j2kcuda_jp2_params* p,
+                     uint8_t** out, size_t* out_len);
+
 /* ---- stage entry points (host arrays in/out; what the parity tests drive, one stage at a
  *      time, the way ext/grok's OPJ_PLUGIN_STATE_DEBUG_ENCODE cross-check does) -------------- */
 /* RCT / ICT on three int32 planes (inverse ICT: float32 bit patterns). mct.cpp:94-471 */

@@ -42,6 +42,34 @@ class Info(C.Structure):
                 ("codestream_length", C.c_uint64)]
 
 
+JP2_MAX_CHANNELS = 16
+
+
+class Jp2Info(C.Structure):
+    _fields_ = [("is_jp2", C.c_uint32), ("brand", C.c_uint32), ("minversion", C.c_uint32),
+                ("width", C.c_uint32), ("height", C.c_uint32), ("ncomp", C.c_uint32),
+                ("bpc", C.c_uint32), ("unk_c", C.c_uint32), ("ipr", C.c_uint32),
+                ("bpcc", C.c_uint32 * JP2_MAX_CHANNELS), ("colr_method", C.c_uint32),
+                ("enumcs", C.c_uint32), ("precedence", C.c_uint32), ("approx", C.c_uint32),
+                ("icc_offset", C.c_uint64), ("icc_length", C.c_uint64), ("cdef_n", C.c_uint32),
+                ("cdef_cn", C.c_uint16 * JP2_MAX_CHANNELS), ("cdef_typ", C.c_uint16 * JP2_MAX_CHANNELS),
+                ("cdef_asoc", C.c_uint16 * JP2_MAX_CHANNELS), ("pclr_entries", C.c_uint32),
+                ("pclr_channels", C.c_uint32), ("pclr_depth", C.c_uint8 * JP2_MAX_CHANNELS),
+                ("pclr_offset", C.c_uint64), ("cmap_n", C.c_uint32),
+                ("cmap_cmp", C.c_uint16 * JP2_MAX_CHANNELS), ("cmap_mtyp", C.c_uint8 * JP2_MAX_CHANNELS),
+                ("cmap_pcol", C.c_uint8 * JP2_MAX_CHANNELS), ("has_capture_res", C.c_uint32),
+                ("has_display_res", C.c_uint32), ("capture_res", C.c_double * 2),
+                ("display_res", C.c_double * 2), ("codestream_offset", C.c_uint64),
+                ("codestream_length", C.c_uint64)]
+
+
+class Jp2Params(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("ncomp", C.c_uint32),
+                ("prec", C.c_uint32 * JP2_MAX_CHANNELS), ("sgnd", C.c_uint32 * JP2_MAX_CHANNELS),
+                ("enumcs", C.c_uint32), ("icc", C.c_char_p), ("icc_len", C.c_size_t),
+                ("alpha_comp", C.c_int32)]
+
+
 class BlockResult(C.Structure):
     _fields_ = [("data", C.POINTER(C.c_uint8)), ("numbps", C.c_int32), ("npasses", C.c_int32),
                 ("rates", C.POINTER(C.c_int32)), ("dist", C.POINTER(C.c_double))]

@@ -76,6 +76,10 @@ static void ensure_init() {
 }
 
 void ref_set_verbose(int v) { g_verbose = v; }
+/* JP2 wrapper for the next ref_encode calls: on = write a JP2 file instead of a raw codestream,
+ * alpha_comp >= 0 marks that component as opacity (-> cdef box, jp2.cpp:2166-2230). */
+static int g_jp2 = 0, g_alpha = -1;
+void ref_set_jp2(int on, int alpha_comp) { g_jp2 = on; g_alpha = alpha_comp; }
 const char* ref_version(void) { return opj_version(); }
 
 /* Whole-frame encode through grok's public API.  planes[c] = w*h int32 samples (unsigned
@@ -94,6 +98,7 @@ int ref_encode(const int32_t* const* planes, int ncomp, int w, int h, int prec, 
     if (!image) return 1;
     image->x0 = image->y0 = 0; image->x1 = w; image->y1 = h;
     for (int i = 0; i < ncomp; ++i) memcpy(image->comps[i].data, planes[i], sizeof(int32_t) * (size_t)w * h);
+    if (g_jp2 && g_alpha >= 0 && g_alpha < ncomp) image->comps[g_alpha].alpha = 1;
 
     opj_cparameters_t params;
     opj_set_default_encoder_parameters(&params);
@@ -120,7 +125,7 @@ int ref_encode(const int32_t* const* planes, int ncomp, int w, int h, int prec, 
     int rc = 2;
     MemOut mo;
     opj_stream_t* stream = opj_stream_create(1 << 20, false);
-    opj_codec_t* codec = opj_create_compress(OPJ_CODEC_J2K);
+    opj_codec_t* codec = opj_create_compress(g_jp2 ? OPJ_CODEC_JP2 : OPJ_CODEC_J2K);
     if (stream && codec) {
         opj_stream_set_user_data(stream, &mo, NULL);
         opj_stream_set_read_function(stream, mo_read);
