@@ -61,6 +61,63 @@ void CudaCodec::GetFileInfo(InputFile &file, FileInfo &info)
 	info.format = (hdr.is_jp2 ? JP2 : J2C);
 	info.colorSpace = (hdr.ncomp >= 3 ? sRGB : sLUM);
 	info.alpha = (hdr.ncomp == 2 || hdr.ncomp == 4 ? STRAIGHT : NO_ALPHA);
+
+	if(hdr.is_jp2)
+	{
+		// the JP2 header boxes, as OpenJPEGCodec::GetFileInfo takes them from opj_read_header_ex (j2k_openjpeg_codec.cpp:303-408)
+		j2kcuda_jp2_info jp2;
+		Check( j2kcuda_probe_jp2(&bytes[0], bytes.size(), &jp2) );
+
+		if(jp2.brand == 0x6a707820)               // 'jpx '
+			info.format = JPX;
+
+		enum { CS_CMYK = 12, CS_sRGB = 16, CS_GRAY = 17, CS_sYCC = 18, CS_esYCC = 19 };
+		if(jp2.colr_method == 1)
+			info.colorSpace = (jp2.enumcs == CS_CMYK ? CMYK : jp2.enumcs == CS_sRGB ? sRGB : jp2.enumcs == CS_GRAY ? sLUM :
+								jp2.enumcs == CS_sYCC ? sYCC : jp2.enumcs == CS_esYCC ? esYCC : UNKNOWN_COLOR_SPACE);
+		else if((jp2.colr_method == 2 || jp2.colr_method == 3) && jp2.icc_length > 0)
+		{
+			info.iccProfile = malloc(jp2.icc_length);      // freed by RGBAinputFile (j2k_rgba_file.cpp:50-54)
+			if(info.iccProfile == NULL)
+				throw Exception("out of memory");
+			info.profileLen = jp2.icc_length;
+			memcpy(info.iccProfile, &bytes[jp2.icc_offset], jp2.icc_length);
+			info.colorSpace = (hdr.ncomp >= 3 ? iccRGB : hdr.ncomp == 1 ? iccLUM : iccANY);
+		}
+
+		if(jp2.cdef_n)
+		{
+			info.alpha = NO_ALPHA;
+			for(unsigned int i=0; i < jp2.cdef_n && i < J2K_CODEC_MAX_CHANNELS; i++)
+			{
+				if(jp2.cdef_cn[i] >= J2K_CODEC_MAX_CHANNELS)
+					continue;
+				// colour asoc 1..3 -> R, G, B; opacity (typ 1 straight, typ 2 premultiplied) -> ALPHA
+				if(jp2.cdef_typ[i] == 0 && jp2.cdef_asoc[i] >= 1 && jp2.cdef_asoc[i] <= 3)
+					info.channelMap[jp2.cdef_cn[i]] = (jp2.cdef_asoc[i] == 1 ? RED : jp2.cdef_asoc[i] == 2 ? GREEN : BLUE);
+				else if(jp2.cdef_typ[i] == 1 || jp2.cdef_typ[i] == 2)
+				{
+					info.channelMap[jp2.cdef_cn[i]] = ALPHA;
+					info.alpha = (jp2.cdef_typ[i] == 2 ? PREMULTIPLIED : STRAIGHT);
+				}
+			}
+		}
+
+		if(jp2.pclr_entries && jp2.pclr_entries <= J2K_CODEC_MAX_LUT_ENTRIES && jp2.pclr_channels <= J2K_CODEC_MAX_CHANNELS)
+		{
+			std::vector<uint32_t> entries(jp2.pclr_entries * jp2.pclr_channels);
+			if(j2kcuda_jp2_palette(&bytes[0], bytes.size(), &entries[0], entries.size()) < 0)
+				throw Exception(j2kcuda_last_error());
+			info.LUTsize = jp2.pclr_entries;
+			for(unsigned int e=0; e < jp2.pclr_entries; e++)
+				for(unsigned int c=0; c < jp2.pclr_channels; c++)
+					info.LUT[e].channel[c] = static_cast<unsigned char>(entries[e * jp2.pclr_channels + c]);
+			for(unsigned int i=0; i < jp2.cmap_n && i < J2K_CODEC_MAX_CHANNELS; i++)
+				if(jp2.cmap_mtyp[i] == 1 && jp2.cmap_pcol[i] < J2K_CODEC_MAX_CHANNELS)
+					info.LUTmap[i] = info.channelMap[jp2.cmap_pcol[i]];
+		}
+	}
+
 	info.settings.reversible = hdr.reversible;
 	info.settings.layers = hdr.numlayers;
 	info.settings.tileSize = (hdr.tiles_x * hdr.tiles_y > 1 ? hdr.tile_w : 0);
@@ -128,7 +185,38 @@ void CudaCodec::WriteFile(OutputFile &file, const FileInfo &info, const Buffer &
 	size_t out_len = 0;
 	Check( j2kcuda_encode(&p, planes, buffer.channels, &out, &out_len) );
 
-	const size_t written = file.Write(out, out_len);      // one contiguous codestream, one Write
+	if(info.format == JP2 || info.format == JPX)
+	{
+		// JP2 boxes around the codestream (the OpenJPEG path of the reference writes raw J2K only: jp2 is a "TODO" there,
+		// j2k_openjpeg_codec.cpp:613-614; the boxes are those opj_jp2_setup_encoder would produce)
+		j2kcuda_jp2_params w;
+		memset(&w, 0, sizeof(w));
+		w.width = info.width;
+		w.height = info.height;
+		w.ncomp = buffer.channels;
+		for(int i=0; i < buffer.channels; i++)
+		{
+			w.prec[i] = info.depth;
+			w.sgnd[i] = 0;
+		}
+		w.enumcs = (buffer.channels >= 3 ? 16 : 17);
+		if(info.iccProfile != NULL && info.profileLen > 0 && !IssRGBProfile(info.iccProfile, info.profileLen))
+		{
+			w.icc = static_cast<const uint8_t *>(info.iccProfile);
+			w.icc_len = info.profileLen;
+		}
+		w.alpha_comp = (info.alpha != NO_ALPHA && (buffer.channels == 2 || buffer.channels == 4) ? buffer.channels - 1 : -1);
+
+		uint8_t *boxed = NULL;
+		size_t boxed_len = 0;
+		const int rc = j2kcuda_wrap_jp2(out, out_len, &w, &boxed, &boxed_len);
+		j2kcuda_free(out);
+		Check(rc);
+		out = boxed;
+		out_len = boxed_len;
+	}
+
+	const size_t written = file.Write(out, out_len);      // one contiguous file image, one Write
 	j2kcuda_free(out);
 
 	if(written != out_len)
