@@ -29,7 +29,7 @@ k_t1_decode(const T1DecBlock* __restrict__ blocks, int nblocks, const T1Tables* 
     __shared__ uint8_t s_sc[256];
     __shared__ uint32_t s_mq[96];
     for (int i = threadIdx.x; i < 2048; i += blockDim.x) s_zc[i] = tab->zc9[i];
-    for (int i = threadIdx.x; i < 256; i += blockDim.x) s_sc[i] = tab->sc[i];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) s_sc[i] = sc_entry(tab->sc, i);
     if (threadIdx.x < 94) s_mq[threadIdx.x] = mq_state_word(tab->mq, threadIdx.x);
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

@@ -132,11 +132,16 @@ J2K_HD inline void scatter(u64* rows, uint32_t nib, int x) {
     for (int r = 0; r < 4; ++r) rows[r] |= (u64)((nib >> r) & 1u) << x;
 }
 
-// sign-coding table index from the 9-bit significance and sign neighbourhoods (bits 1 N, 3 W, 5 E, 7 S)
+// Sign-coding table index from the 9-bit significance and sign neighbourhoods (bits 1 N, 3 W, 5 E, 7 S): the
+// significance bits go to the even positions, the sign bits stay on the odd ones, so nothing has to be gathered.
+// sc_entry() gives the table in that order from T1Tables::sc (which is indexed W | E<<1 | N<<2 | S<<3 | signs << 4).
 J2K_HD inline uint32_t sc_index(uint32_t s9, uint32_t g9) {
-    g9 &= s9;
-    return ((s9 >> 3) & 1u) | (((s9 >> 5) & 1u) << 1) | (((s9 >> 1) & 1u) << 2) | (((s9 >> 7) & 1u) << 3) |
-           (((g9 >> 3) & 1u) << 4) | (((g9 >> 5) & 1u) << 5) | (((g9 >> 1) & 1u) << 6) | (((g9 >> 7) & 1u) << 7);
+    return ((s9 >> 1) & 0x55u) | (g9 & s9 & 0xaau);
+}
+J2K_HD inline uint8_t sc_entry(const uint8_t* sc, int i) {
+    const int sN = i & 1, gN = (i >> 1) & 1, sW = (i >> 2) & 1, gW = (i >> 3) & 1, sE = (i >> 4) & 1, gE = (i >> 5) & 1,
+              sS = (i >> 6) & 1, gS = (i >> 7) & 1;
+    return sc[sW | (sE << 1) | (sN << 2) | (sS << 3) | (gW << 4) | (gE << 5) | (gN << 6) | (gS << 7)];
 }
 
 // Per-warp scratch of the stripe being scanned, in column-major form: the row masks are turned into
@@ -162,6 +167,17 @@ J2K_HD inline u64 rowmask(const uint32_t* out, uint32_t o0, uint32_t o1, int b) 
     for (int x = 0; x < 64; ++x) m |= (u64)((out[x] >> b) & 1u) << x;
     return m;
 #endif
+}
+// decisions of a column's member rows in list order -> one bit per stripe row
+J2K_HD inline uint32_t mr_rows(uint32_t res, uint32_t mem4) {
+    uint32_t out = 0;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const uint32_t m = (mem4 >> r) & 1u;
+        out |= (res & m) << r;
+        res >>= m;
+    }
+    return out;
 }
 // nibble -> the window bits of rows 1..4 at column offset 0 (bits 3, 6, 9, 12)
 J2K_HD inline uint32_t spread4(uint32_t n) {
@@ -227,7 +243,19 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
             for (int x = lane; x < 64; x += nlanes) {
                 cb.win[x] = pack_win(S, x);
                 uint32_t a = nibble(memb, x);
-                if (passtype == 1) a |= nibble(&R.ref[ib + 1], x) << 4;
+                if (passtype == 1) {
+                    // magnitude refinement contexts depend on nothing decoded in this pass: the column's list of
+                    // context codes (2 bits each, 1 = MAG, 2 = MAG + 1, 3 = MAG + 2, in row order) is made here
+                    const uint32_t ref4 = nibble(&R.ref[ib + 1], x), w18 = cb.win[x];
+                    uint32_t list = 0, k = 0;
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) {
+                        if (!((a >> r) & 1u)) continue;
+                        const uint32_t code = ((ref4 >> r) & 1u) ? 3u : (((w18 >> (3 * r)) & 0x1efu) ? 2u : 1u);
+                        list |= code << k; k += 2;
+                    }
+                    a |= list << 8;
+                }
                 cb.aux[x] = a;
                 cb.out[x] = 0;
             }
@@ -280,21 +308,17 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
                     }
                 }
             } else if (passtype == 1) {
-                // magnitude refinement: significant and not coded in this plane's first pass
+                // magnitude refinement: significant and not coded in this plane's first pass; decisions come out in
+                // list order and are put back on their rows by the lanes afterwards
                 while (cols) {
                     const int x = J2K_FFSLL(cols) - 1;
                     cols &= cols - 1;
-                    const uint32_t win = cb.win[x];
-                    const uint32_t a = cb.aux[x], mem4 = a & 15u, ref4 = a >> 4;
-                    uint32_t bit4 = 0;
-#pragma unroll 1
-                    for (int r = 0; r < 4; ++r) {
-                        if (!((mem4 >> r) & 1u)) continue;
-                        const uint32_t s9 = (win >> (3 * r)) & 0x1efu;
-                        const uint32_t ctx = ((ref4 >> r) & 1u) ? CTX_MAG + 2 : (s9 ? CTX_MAG + 1 : CTX_MAG);
-                        bit4 |= mq.decode(st, mqtab, ctx) << r;
-                    }
-                    if (bit4) { cb.out[x] = bit4 << 12; any = true; }
+                    uint32_t list = cb.aux[x] >> 8, res = 0, k = 0;
+                    do {
+                        res |= mq.decode(st, mqtab, CTX_MAG - 1 + (list & 3u)) << k;
+                        ++k; list >>= 2;
+                    } while (list);
+                    if (res) { cb.out[x] = res; any = true; }
                 }
             } else {
                 // cleanup: everything not yet significant and not visited
@@ -347,7 +371,13 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
             // ---- results back into the row masks (rows of the neighbouring stripes are unchanged) ----
             uint32_t o0 = 0, o1 = 0;
 #if defined(__CUDA_ARCH__)
-            if (any) { o0 = cb.out[lane]; o1 = cb.out[lane + 32]; }
+            if (any) {
+                o0 = cb.out[lane]; o1 = cb.out[lane + 32];
+                if (passtype == 1) { o0 = mr_rows(o0, cb.aux[lane] & 15u) << 12; o1 = mr_rows(o1, cb.aux[lane + 32] & 15u) << 12; }
+            }
+#else
+            if (any && passtype == 1)
+                for (int x = 0; x < 64; ++x) cb.out[x] = mr_rows(cb.out[x], cb.aux[x] & 15u) << 12;
 #endif
 #pragma unroll
             for (int r = 0; r < 4; ++r) {

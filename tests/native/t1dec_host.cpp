@@ -27,6 +27,8 @@ extern "C" int t1dec_host_block(const uint8_t* data, int len, int w, int h, int 
     for (int i = 0; i < 32; ++i) st[i] = tab[0];
     st[CTX_UNI] = tab[46 * 2]; st[CTX_AGG] = tab[3 * 2]; st[CTX_ZC] = tab[4 * 2];
     static ColBuf cb;
-    decode_block(b, R, cb, st, zc9, sc, tab, seg.data(), 1, 0, 1);
+    uint8_t sc2[256];
+    for (int i = 0; i < 256; ++i) sc2[i] = sc_entry(sc, i);
+    decode_block(b, R, cb, st, zc9, sc2, tab, seg.data(), 1, 0, 1);
     return 0;
 }
