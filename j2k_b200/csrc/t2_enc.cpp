@@ -325,6 +325,116 @@ static bool simulate(const CodingParams& cp, EncTile& t, const std::vector<TileP
     return true;
 }
 
+// ---- rate-capped single layer: the bisection without redoing what cannot have changed ----------
+// The reference redoes layer formation for every block and the Tier-2 simulation of every packet in each of the
+// ~40 bisection steps (tcd.cpp:253-317): for the 26 280 blocks of a DCI 4K frame that is the critical path of the whole
+// encode.  The decisions of one block are comparisons of the threshold with a handful of slopes, so
+// its outcome is known to stay the same while the threshold stays between the largest slope it refused and the smallest
+// one it accepted; a packet's byte count stays the same while none of its blocks changed.  Only the rest is recomputed.
+// Every pass/fail answer is the one the full computation would give, and the final layer is formed by the plain
+// routine, so the codestream is unchanged (tests/test_t2_host.py, tests/test_gpu_configs.py compare it with the reference).
+struct BisectCache {
+    struct Visit { int packet; int kind; };          // kind 0: packet; 1: start of a component; 2: end of a progression
+    std::vector<PacketId> packets;
+    std::vector<Visit> order;
+    std::vector<uint64_t> size;
+    std::vector<uint8_t> dirty;
+    std::vector<int> blk_packet;
+    std::vector<double> lo, hi;                       // per block: thresholds for which its cached layer holds
+    std::vector<uint8_t> valid;
+};
+
+static void bisect_cache_init(const CodingParams& cp, EncTile& t, BisectCache& bc) {
+    // the visiting order of simulate() below, flattened once
+    int ncomp_iter = cp.max_comp_size > 0 ? cp.ncomp : 1;
+    std::vector<PocEntry> pocs = cp.pocs;
+    int maxres = 0;
+    for (int c = 0; c < cp.ncomp; ++c) maxres = std::max(maxres, cp.comps[c].numres);
+    if (pocs.empty()) pocs.push_back(PocEntry{0, 0, cp.numlayers, maxres, cp.ncomp, cp.prog});
+    size_t npoc = cp.rsiz == J2KCUDA_PROFILE_CINEMA_4K ? 2 : 1;
+    npoc = std::min(npoc, pocs.size());
+    std::vector<uint8_t> include;
+    for (int c = 0; c < ncomp_iter; ++c) {
+        bc.order.push_back({-1, 1});
+        for (size_t pi = 0; pi < npoc; ++pi) {
+            const PocEntry& pe = pocs[pi];
+            std::vector<PacketId> pk;
+            if (cp.max_comp_size > 0 && cp.tp_on)
+                progression_packets(cp, t.geo, pe.prg, pe.resno0, pe.resno1, c, c + 1, 0, pe.layno1, include, pk);
+            else
+                progression_packets(cp, t.geo, pe.prg, pe.resno0, pe.resno1, pe.compno0, pe.compno1, 0, pe.layno1, include, pk);
+            for (auto& id : pk) {
+                if (id.layno >= 1) continue;
+                bc.order.push_back({(int)bc.packets.size(), 0});
+                bc.packets.push_back(id);
+            }
+            bc.order.push_back({-1, 2});
+        }
+    }
+    bc.size.assign(bc.packets.size(), 0);
+    bc.dirty.assign(bc.packets.size(), 1);
+    bc.blk_packet.assign(t.blocks.size(), -1);
+    for (size_t i = 0; i < bc.packets.size(); ++i) {
+        const PacketId& id = bc.packets[i];
+        const ResGeo& res = t.geo.comps[id.compno].res[id.resno];
+        for (int b = 0; b < res.numbands; ++b) {
+            const PrecGeo& prc = res.bands[b].precs[id.precno];
+            for (int k = 0; k < prc.cw * prc.ch; ++k) bc.blk_packet[prc.first_cblk + k] = (int)i;
+        }
+    }
+    bc.lo.assign(t.blocks.size(), 0); bc.hi.assign(t.blocks.size(), 0);
+    bc.valid.assign(t.blocks.size(), 0);
+}
+
+// makelayer(cp, t, 0, thresh, false, false) for the blocks whose cached answer may not hold at this threshold
+static void makelayer_cached(EncTile& t, double thresh, BisectCache& bc) {
+    const size_t nb = t.blocks.size();
+    for (size_t i = 0; i < nb; ++i) {
+        if (bc.valid[i] && bc.lo[i] <= thresh && thresh <= bc.hi[i]) continue;
+        EncBlock& cblk = t.blocks[i];
+        EncLayer& layer = cblk.layers[0];
+        cblk.included_other = 0;
+        int n = 0;
+        double min_in = DBL_MAX, max_out = -DBL_MAX;
+        for (int passno = 0; passno < cblk.totalpasses; ++passno) {
+            uint32_t dr; double dd;
+            if (n == 0) { dr = (uint32_t)cblk.rates[passno]; dd = cblk.dist[passno]; }
+            else { dr = (uint32_t)(cblk.rates[passno] - cblk.rates[n - 1]); dd = cblk.dist[passno] - cblk.dist[n - 1]; }
+            if (!dr) { if (dd != 0) n = passno + 1; continue; }
+            const double slope = dd / dr;
+            if (thresh - slope < DBL_EPSILON) { n = passno + 1; if (slope < min_in) min_in = slope; }
+            else if (slope > max_out) max_out = slope;
+        }
+        // same decisions for every threshold in [max_out + 1, min_in]: accepted slopes stay >= it (difference <= 0 <
+        // epsilon), refused ones stay at least 1 below it (difference >= 1 - rounding > epsilon)
+        bc.lo[i] = max_out == -DBL_MAX ? -DBL_MAX : (std::fabs(max_out) < 1e15 ? max_out + 1.0 : DBL_MAX);
+        bc.hi[i] = min_in;
+        const int oldn = bc.valid[i] ? layer.numpasses : -1;
+        bc.valid[i] = 1;
+        layer.numpasses = n;
+        if (!n) layer.disto = 0;
+        else { layer.len = cblk.rates[n - 1]; layer.data_off = 0; layer.disto = cblk.dist[n - 1]; }
+        if (oldn != n && bc.blk_packet[i] >= 0) bc.dirty[bc.blk_packet[i]] = 1;
+    }
+}
+
+// simulate(cp, t, parts, 1, maxlen): the same checks in the same order on byte counts that are recomputed only for
+// packets with a changed block
+static bool simulate_cached(const CodingParams& cp, EncTile& t, uint64_t maxlen, BisectCache& bc) {
+    for (size_t i = 0; i < bc.packets.size(); ++i)
+        if (bc.dirty[i]) { bc.size[i] = encode_packet(cp, t, bc.packets[i], nullptr); bc.dirty[i] = 0; }
+    int64_t remaining = (int64_t)maxlen;
+    uint64_t comp_len = 0;
+    for (const auto& v : bc.order) {
+        if (v.kind == 1) { comp_len = 0; continue; }
+        if (v.kind == 2) { if (cp.max_comp_size && comp_len > cp.max_comp_size) return false; continue; }
+        const uint64_t n = bc.size[v.packet];
+        if ((int64_t)n > remaining) return false;
+        comp_len += n; remaining -= (int64_t)n;
+    }
+    return true;
+}
+
 // tcd.cpp:165-319
 static void pcrd_bisect(const CodingParams& cp, EncTile& t, const std::vector<TilePart>& parts,
                         const double* rates, uint64_t len) {
@@ -346,12 +456,16 @@ static void pcrd_bisect(const CodingParams& cp, EncTile& t, const std::vector<Ti
         bool all = false;
         if (rates[layno] > 0.0) {
             double thresh = 0;
+            const bool cached = cp.numlayers == 1 && !(cp.csty & 2);     // SOP packet numbers depend on the visiting history
+            BisectCache bc;
+            if (cached) bisect_cache_init(cp, t, bc);
             for (int i = 0; i < 128; ++i) {
                 thresh = (lo + hi) / 2;
-                makelayer(cp, t, layno, thresh, false, false);
+                if (cached) makelayer_cached(t, thresh, bc);
+                else makelayer(cp, t, layno, thresh, false, false);
                 if (std::fabs(old_thresh - thresh) < 0.001) break;
                 old_thresh = thresh;
-                if (!simulate(cp, t, parts, layno + 1, maxlen)) { lo = thresh; continue; }
+                if (!(cached ? simulate_cached(cp, t, maxlen, bc) : simulate(cp, t, parts, layno + 1, maxlen))) { lo = thresh; continue; }
                 hi = thresh;
             }
             goodthresh = (hi == 0) ? thresh : hi;

@@ -1,0 +1,168 @@
+"""Throughput of every BASELINE.json configuration (C1-C5) through the C ABI with pinned HOST buffers (end to end:
+H2D, device stages, D2H, host Tier-2), one process per GPU.  Prints one JSON line per configuration.
+
+  python tools/bench_configs.py [--reps 3] [--kind smooth]
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tools/bench_configs.py
+
+C1-C3, C5: frames of a sequence, frame f -> rank f % N (no collective).  C4: the 40 tiles of each 8K frame are split in
+contiguous ranges over the ranks (j2kcuda_params.tile_first / tile_count); the fragments are gathered to rank 0 with
+torch.distributed and joined there (j2kcuda_join_tile_streams) -- the one collective of the design, outside the kernels.
+Every decoded frame is compared with its source (lossless configs) before the numbers are printed."""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+import time
+import numpy as np
+
+ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--reps", type=int, default=3)
+    ap.add_argument("--kind", default="smooth")
+    ap.add_argument("--workers", type=int, default=8)
+    ap.add_argument("--only", default="")
+    args = ap.parse_args()
+    import torch
+    import torch.distributed as dist
+    import j2k
+    from j2k_b200 import _lib as L
+    from j2k_b200.frames import make_frame, shard_frames, shard_tiles
+    from j2k_b200.sharding import gather_bytes, join_tile_streams
+
+    rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib = L.lib()
+    lib.j2kcuda_sequence_create.restype = C.c_void_p
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def maxtime(dt):
+        if world == 1:
+            return dt
+        t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def pinned(frames):
+        out = []
+        for f in frames:
+            t = torch.empty(f.shape, dtype=torch.uint8 if f.dtype == np.uint8 else torch.uint16).pin_memory()
+            t.numpy()[...] = f
+            out.append(t)
+        return out
+
+    def table(tensors):
+        keep = [j2k.planes_of(t.numpy()) for t in tensors]
+        return (C.POINTER(L.Plane) * len(keep))(*[C.cast(k, C.POINTER(L.Plane)) for k in keep]), keep
+
+    def run_sequence(name, h, w, nc, prec, frames_per_rank, lossless, **kw):
+        """frames sharded over ranks; returns encode / decode MPix/s of the whole job"""
+        dt = np.uint8 if prec <= 8 else np.uint16
+        mine = shard_frames(frames_per_rank * world, rank, world)
+        src = pinned([make_frame(h, w, nc, prec, args.kind, seed=f).astype(dt) for f in mine])
+        dst = pinned([np.zeros((h, w, nc), dt) for _ in mine])
+        F = len(mine)
+        p = L.default_params(width=w, height=h, ncomp=nc, prec=prec, **kw)
+        seq = C.c_void_p(lib.j2kcuda_sequence_create(C.byref(p), local, args.workers))
+        tin, k1 = table(src); tout, k2 = table(dst)
+        outs = (C.POINTER(C.c_uint8) * F)(); lens = (C.c_size_t * F)()
+        te = td = 0.0
+        for rep in range(args.reps + 1):
+            barrier(); t0 = time.perf_counter()
+            assert lib.j2kcuda_sequence_encode(seq, tin, F, nc, 0, outs, lens) == 0, L.last_error()
+            barrier(); t1 = time.perf_counter()
+            assert lib.j2kcuda_sequence_decode(seq, C.cast(outs, C.POINTER(C.POINTER(C.c_uint8))), lens, F, 0, tout, nc, 0) == 0, L.last_error()
+            barrier(); t2 = time.perf_counter()
+            if rep:                                   # the first pass creates the contexts
+                te += maxtime(t1 - t0); td += maxtime(t2 - t1)
+            nbytes = sum(lens[i] for i in range(F))
+            if rep < args.reps:
+                for i in range(F):
+                    lib.j2kcuda_free(outs[i])
+        ok = True
+        if lossless:
+            ok = all(bool((a == b).all()) for a, b in zip(src, dst))
+        else:
+            worst = max(float((a.to(torch.int32) - b.to(torch.int32)).abs().max()) for a, b in zip(src, dst))
+            ok = worst < (1 << prec) / 8              # rate-capped: sanity only, parity is tests/test_gpu_configs.py
+        for i in range(F):
+            lib.j2kcuda_free(outs[i])
+        lib.j2kcuda_sequence_destroy(seq)
+        mp = args.reps * F * world * w * h / 1e6
+        return {"config": name, "n_gpus": world, "frames_per_step": F * world, "encode_mpix_s": mp / te, "decode_mpix_s": mp / td,
+                "roundtrip_mpix_s": mp / (te + td), "codestream_bytes_per_frame": nbytes / F, "verified": ok,
+                "sharding": "frames over ranks, no collective"}
+
+    def run_tiles(name, h, w, nc, prec, tile, nframes):
+        """C4: tiles of one frame sharded over the ranks, fragments gathered and joined on rank 0"""
+        frames = [make_frame(h, w, nc, prec, args.kind, seed=100 + f) for f in range(nframes)]
+        src = pinned(frames)
+        tx, ty = -(-w // tile), -(-h // tile)
+        first, last = shard_tiles(tx * ty, rank, world)
+        count = last - first
+        p = L.default_params(width=w, height=h, ncomp=nc, prec=prec, mct=1, tile_w=tile, tile_h=tile, tile_first=first, tile_count=count if world > 1 else 0)
+        whole = L.default_params(width=w, height=h, ncomp=nc, prec=prec, mct=1, tile_w=tile, tile_h=tile)
+        lib.j2kcuda_encoder_create.restype = C.c_void_p
+        enc = C.c_void_p(lib.j2kcuda_encoder_create(C.byref(p)))
+        assert enc.value, L.last_error()
+        te = 0.0
+        streams = []
+        for rep in range(args.reps + 1):
+            streams = []
+            barrier(); t0 = time.perf_counter()
+            for t in src:
+                pl = j2k.planes_of(t.numpy())
+                out = C.POINTER(C.c_uint8)(); n = C.c_size_t(0)
+                assert lib.j2kcuda_encoder_upload(enc, pl, nc) == 0, L.last_error()
+                assert lib.j2kcuda_encoder_run(enc) == 0, L.last_error()
+                assert lib.j2kcuda_encoder_finish(enc, C.byref(out), C.byref(n)) == 0, L.last_error()
+                frag = C.string_at(out, n.value); lib.j2kcuda_free(out)
+                if world > 1:
+                    parts = gather_bytes(frag, device="cuda")          # the one exchange step: tile bitstreams of all ranks
+                    if rank == 0:
+                        streams.append(join_tile_streams(whole, parts))
+                else:
+                    streams.append(frag)
+            barrier(); t1 = time.perf_counter()
+            if rep:
+                te += maxtime(t1 - t0)
+        lib.j2kcuda_encoder_destroy(enc)
+        ok = True
+        if rank == 0:
+            ok = bool(np.array_equal(j2k.decode(streams[0]), frames[0]))
+        mp = args.reps * nframes * w * h / 1e6
+        return {"config": name, "n_gpus": world, "frames_per_step": nframes, "encode_mpix_s": mp / te, "verified": ok,
+                "codestream_bytes_per_frame": len(streams[0]) if streams else None,
+                "sharding": "tiles of each frame over ranks (contiguous ranges), fragments gathered to rank 0 and joined"}
+
+    jobs = [
+        ("C1", lambda: run_sequence("C1 2048x1080 8-bit RGB lossless 5/3", 1080, 2048, 3, 8, 16, True, mct=1)),
+        ("C2", lambda: run_sequence("C2 4096x2160 16-bit RGBA lossless 5/3", 2160, 4096, 4, 16, 8, True, mct=1)),
+        ("C3", lambda: run_sequence("C3 DCI 4K 12-bit XYZ 9/7 ICT cinema profile (PCRD rate cap)", 2160, 4096, 3, 12, 8, False,
+                                    irreversible=1, mct=1, profile=L.PROFILE_CINEMA_4K)),
+        ("C4", lambda: run_tiles("C4 8192x4320 16-bit RGB lossless, 1024x1024 tiles", 4320, 8192, 3, 16, 1024, 2)),
+        ("C5", lambda: run_sequence("C5 4096x2160 16-bit RGB lossless sequence", 2160, 4096, 3, 16, 16, True, mct=1)),
+    ]
+    for key, fn in jobs:
+        if args.only and key not in args.only.split(","):
+            continue
+        r = fn()
+        if rank == 0:
+            print(json.dumps(r), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
