@@ -127,13 +127,14 @@ def main():
                 assert lib.j2kcuda_encoder_upload(enc, pl, nc) == 0, L.last_error()
                 assert lib.j2kcuda_encoder_run(enc) == 0, L.last_error()
                 assert lib.j2kcuda_encoder_finish(enc, C.byref(out), C.byref(n)) == 0, L.last_error()
-                frag = C.string_at(out, n.value); lib.j2kcuda_free(out)
                 if world > 1:
-                    parts = gather_bytes(frag, device="cuda")          # the one exchange step: tile bitstreams of all ranks
+                    frag = np.ctypeslib.as_array(out, shape=(n.value,))                  # the library's buffer, not a copy
+                    parts = gather_bytes(frag, device="cuda", dst=0, as_arrays=True)   # the one exchange step: tile bitstreams to rank 0
                     if rank == 0:
                         streams.append(join_tile_streams(whole, parts))
                 else:
-                    streams.append(frag)
+                    streams.append(C.string_at(out, n.value))
+                lib.j2kcuda_free(out)
             barrier(); t1 = time.perf_counter()
             if rep:
                 te += maxtime(t1 - t0)
