@@ -101,6 +101,7 @@ int j2kcuda_sequence_encode(j2kcuda_sequence* s, const j2kcuda_plane* const* fra
     while ((int)s->enc.size() < nw) {            // contexts are created once and reused by later calls
         j2kcuda_encoder* e = j2kcuda_encoder_create(&s->params);
         if (!e) return J2KCUDA_ERR_PARAM;        // message already set
+        encoder_set_throughput_mode(e, s->nworkers > 2);
         s->enc.push_back(e);
     }
     for (int i = 0; i < nframes; ++i) { outs[i] = nullptr; out_lens[i] = 0; }

@@ -6,3 +6,9 @@ namespace j2k {
 std::string& last_error();                       // thread-local
 int set_error(int code, const std::string& msg); // stores msg, returns code
 }  // namespace j2k
+
+// Internal (not exported through include/j2kcuda.h): shape of the MQ kernel.  A lone frame wants few blocks per warp
+// (the kernel ends when its longest chain ends); with many frames in flight the device is bound by issue slots and
+// fuller warps do the same work with fewer of them.  api_batch.cpp tells its contexts which regime they are in.
+struct j2kcuda_encoder;
+namespace j2k { void encoder_set_throughput_mode(::j2kcuda_encoder* e, bool many_frames_in_flight); }

@@ -199,6 +199,7 @@ static int setup_encoder(j2kcuda_encoder* e) {
         CK(cudaMallocHost(&e->h_offsets, ((size_t)e->nblocks + 1) * sizeof(uint32_t)));
     }
     e->dist.assign(e->nblocks, {});
+    e->mq_lanes = e->nblocks >= 4096 ? 8 : 4;
     if (const char* s = getenv("J2KCUDA_MQ_LANES")) { int v = atoi(s); if (v >= 1 && v <= 32) e->mq_lanes = v; }
     if (const char* s = getenv("J2KCUDA_MQ_NLONG")) e->mq_nlong = atoi(s);
     // sample conversion parameters
@@ -483,3 +484,10 @@ int j2kcuda_encode(const j2kcuda_params* p, const j2kcuda_plane* planes, int npl
 }
 
 }  // extern "C"
+
+namespace j2k {
+void encoder_set_throughput_mode(::j2kcuda_encoder* e, bool many) {
+    if (!e || getenv("J2KCUDA_MQ_LANES")) return;
+    e->mq_lanes = many ? 16 : (e->nblocks >= 4096 ? 8 : 4);
+}
+}  // namespace j2k

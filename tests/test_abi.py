@@ -27,6 +27,7 @@ def test_exports_every_declared_symbol():
 def test_struct_sizes_match_header():
     # sizes printed by a C program compiled against include/j2kcuda.h (gcc, x86-64)
     assert (C.sizeof(L.Plane), C.sizeof(L.Params), C.sizeof(L.Info)) == (40, 232, 144)
+    assert (C.sizeof(L.Jp2Info), C.sizeof(L.Jp2Params)) == (400, 168)
     p = L.default_params()
     assert (p.numresolution, p.cblk_w, p.cblk_h, p.numlayers, p.device) == (6, 64, 64, 1, -1)
 
