@@ -51,7 +51,7 @@ int j2kcuda_init(int device, j2kcuda_log_fn, void*) {
     return J2KCUDA_OK;
 }
 
-void j2kcuda_shutdown(void) {}
+void j2kcuda_shutdown(void) { j2k::out_release_all(); }
 
 int j2kcuda_stage_mct(int32_t* c0, int32_t* c1, int32_t* c2, size_t n, int irreversible, int inverse) {
     if (!c0 || !c1 || !c2) return set_error(J2KCUDA_ERR_PARAM, "null plane");

@@ -12,7 +12,7 @@ extern "C" {
 
 int j2kcuda_version(void) { return J2KCUDA_VERSION; }
 const char* j2kcuda_last_error(void) { return j2k::last_error().c_str(); }
-void j2kcuda_free(void* p) { free(p); }
+void j2kcuda_free(void* p) { j2k::out_free(p); }
 
 void j2kcuda_default_params(j2kcuda_params* p) {   // openjpeg.cpp:706-728
     if (!p) return;
@@ -81,10 +81,11 @@ int j2kcuda_t2_assemble(const j2kcuda_params* p, const j2kcuda_block_result* blo
         }
     }
     if (k != nblocks) return set_error(J2KCUDA_ERR_PARAM, "block count mismatch");
-    std::vector<uint8_t> cs;
+    static thread_local std::vector<uint8_t> cs;     // keeps its pages between frames
+    cs.clear();
     std::string err;
     if (!host.assemble(tiles, cs, err)) return set_error(J2KCUDA_ERR_PARAM, err);
-    *out = (uint8_t*)malloc(cs.size() ? cs.size() : 1);
+    *out = (uint8_t*)out_alloc(cs.size());
     if (!*out) return set_error(J2KCUDA_ERR_NOMEM, "malloc");
     memcpy(*out, cs.data(), cs.size());
     *out_len = cs.size();
@@ -96,10 +97,11 @@ int j2kcuda_join_tile_streams(const j2kcuda_params* p, const uint8_t* const* fra
     if (!p || !frags || !lens || !out || !out_len || nfrags < 0) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     CodingParams cp;
     setup_coding_params(*p, cp);
-    std::vector<uint8_t> cs;
+    static thread_local std::vector<uint8_t> cs;     // keeps its pages between frames
+    cs.clear();
     std::string err;
     if (!join_tile_streams(cp, frags, lens, nfrags, cs, err)) return set_error(J2KCUDA_ERR_PARAM, err);
-    *out = (uint8_t*)malloc(cs.size() ? cs.size() : 1);
+    *out = (uint8_t*)out_alloc(cs.size());
     if (!*out) return set_error(J2KCUDA_ERR_NOMEM, "malloc");
     memcpy(*out, cs.data(), cs.size());
     *out_len = cs.size();

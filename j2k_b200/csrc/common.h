@@ -1,10 +1,15 @@
 // Error plumbing shared by the C-ABI translation units.
 #pragma once
+#include <cstddef>
 #include <string>
 
 namespace j2k {
 std::string& last_error();                       // thread-local
 int set_error(int code, const std::string& msg); // stores msg, returns code
+// every buffer the library hands out for j2kcuda_free(); large ones are recycled (common.cpp)
+void* out_alloc(size_t n);
+void out_free(void* p);
+void out_release_all();                          // j2kcuda_shutdown
 }  // namespace j2k
 
 // Internal (not exported through include/j2kcuda.h): shape of the MQ kernel.  A lone frame wants few blocks per warp

@@ -430,9 +430,9 @@ int j2kcuda_t2_parse(const uint8_t* bytes, size_t n, unsigned reduce, int32_t** 
     (void)reduce;
     size_t total = 0; int nb = 0;
     for (auto& t : h.tiles) for (auto& b : t.blocks) { total += (size_t)b.len; ++nb; }
-    int32_t* info = (int32_t*)malloc(sizeof(int32_t) * 4 * (size_t)(nb ? nb : 1));
-    uint8_t* data = (uint8_t*)malloc(total ? total : 1);
-    if (!info || !data) { free(info); free(data); return set_error(J2KCUDA_ERR_NOMEM, "malloc"); }
+    int32_t* info = (int32_t*)out_alloc(sizeof(int32_t) * 4 * (size_t)(nb ? nb : 1));
+    uint8_t* data = (uint8_t*)out_alloc(total);
+    if (!info || !data) { out_free(info); out_free(data); return set_error(J2KCUDA_ERR_NOMEM, "malloc"); }
     size_t pos = 0; int k = 0;
     for (auto& t : h.tiles)
         for (auto& b : t.blocks) {

@@ -448,10 +448,11 @@ int j2kcuda_encoder_finish(j2kcuda_encoder* e, uint8_t** out, size_t* out_len) {
     EncoderHost host;
     host.cp = cp;
     host.ntiles = (int)e->tiles.size();
-    std::vector<uint8_t> cs;
+    static thread_local std::vector<uint8_t> cs;     // keeps its pages between frames
+    cs.clear();
     std::string err;
     if (!host.assemble(e->tiles, cs, err)) return set_error(J2KCUDA_ERR_PARAM, err);
-    *out = (uint8_t*)malloc(cs.size() ? cs.size() : 1);
+    *out = (uint8_t*)out_alloc(cs.size());
     if (!*out) return set_error(J2KCUDA_ERR_NOMEM, "malloc");
     memcpy(*out, cs.data(), cs.size());
     *out_len = cs.size();

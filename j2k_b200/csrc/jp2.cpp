@@ -234,7 +234,7 @@ int j2kcuda_wrap_jp2(const uint8_t* cs, size_t len, const j2kcuda_jp2_params* p,
     }
     // contiguous codestream box with its real length (jp2.cpp:1976-2011)
     put((uint32_t)(len + 8), 4); put(BOX_JP2C, 4);
-    uint8_t* buf = (uint8_t*)malloc(v.size() + len);
+    uint8_t* buf = (uint8_t*)out_alloc(v.size() + len);
     if (!buf) return set_error(J2KCUDA_ERR_NOMEM, "out of memory");
     memcpy(buf, v.data(), v.size());
     memcpy(buf + v.size(), cs, len);

@@ -56,8 +56,9 @@ def gather_bytes(blob, device="cpu", group=None, dst=None, as_arrays=False):
     return parts if as_arrays else [p.tobytes() for p in parts]
 
 
-def join_tile_streams(params, fragments):
-    """fragments: tile-part byte strings of all ranks (any order) -> the frame's codestream (j2kcuda_join_tile_streams)"""
+def join_tile_streams(params, fragments, length_only=False):
+    """fragments: tile-part byte strings of all ranks (any order) -> the frame's codestream (j2kcuda_join_tile_streams);
+    length_only: join, then give the buffer straight back to the library (a writer would hand it to the file instead)"""
     import ctypes as C
     from . import _lib as L
     frags = [f for f in fragments if len(f)]
@@ -70,6 +71,9 @@ def join_tile_streams(params, fragments):
     rc = L.lib().j2kcuda_join_tile_streams(C.byref(params), ptrs, lens, len(frags), C.byref(out), C.byref(n))
     if rc:
         raise RuntimeError("j2kcuda_join_tile_streams: " + L.last_error())
+    if length_only:
+        L.lib().j2kcuda_free(out)
+        return n.value
     data = C.string_at(out, n.value)
     L.lib().j2kcuda_free(out)
     return data
