@@ -27,6 +27,7 @@ def main():
     ap.add_argument("--kind", default="smooth")
     ap.add_argument("--workers", type=int, default=8)
     ap.add_argument("--only", default="")
+    ap.add_argument("--frames8k", type=int, default=4)
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -118,9 +119,34 @@ def main():
         assert enc.value, L.last_error()
         te = 0.0
         streams = []
+        phases = [0.0, 0.0, 0.0, 0.0]
+        import queue
+        import threading
+
+        def exchange(q, rep, streams):
+            """gather + join of finished fragments, on its own thread: the exchange of frame f overlaps the encode of f+1"""
+            torch.cuda.set_device(local)
+            while True:
+                item = q.get()
+                if item is None:
+                    return
+                out, n = item
+                tc = time.perf_counter()
+                frag = np.ctypeslib.as_array(out, shape=(n,))                          # the library's buffer, not a copy
+                parts = gather_bytes(frag, device="cuda", dst=0, as_arrays=True)       # the one exchange step: tile bitstreams to rank 0
+                td = time.perf_counter()
+                if rank == 0:                                                          # a Python copy of the file only for the final check
+                    streams.append(join_tile_streams(whole, parts, length_only=rep < args.reps))
+                lib.j2kcuda_free(out)
+                phases[2] = td - tc; phases[3] = time.perf_counter() - td
+
         for rep in range(args.reps + 1):
             streams = []
+            q = queue.Queue()
+            th = None
             barrier(); t0 = time.perf_counter()
+            if world > 1:
+                th = threading.Thread(target=exchange, args=(q, rep, streams)); th.start()
             for t in src:
                 pl = j2k.planes_of(t.numpy())
                 out = C.POINTER(C.c_uint8)(); n = C.c_size_t(0)
@@ -129,18 +155,14 @@ def main():
                 assert lib.j2kcuda_encoder_run(enc) == 0, L.last_error()
                 tb = time.perf_counter()
                 assert lib.j2kcuda_encoder_finish(enc, C.byref(out), C.byref(n)) == 0, L.last_error()
-                tc = time.perf_counter()
+                phases[0] = tb - ta; phases[1] = time.perf_counter() - tb
                 if world > 1:
-                    frag = np.ctypeslib.as_array(out, shape=(n.value,))                  # the library's buffer, not a copy
-                    parts = gather_bytes(frag, device="cuda", dst=0, as_arrays=True)   # the one exchange step: tile bitstreams to rank 0
-                    td = time.perf_counter()
-                    if rank == 0:                                            # a Python copy of the file only for the final check
-                        streams.append(join_tile_streams(whole, parts, length_only=rep < args.reps))
+                    q.put((out, n.value))
                 else:
-                    td = time.perf_counter()
                     streams.append(C.string_at(out, n.value) if rep == args.reps else n.value)
-                lib.j2kcuda_free(out)
-                phases = [tb - ta, tc - tb, td - tc, time.perf_counter() - td]
+                    lib.j2kcuda_free(out)
+            if th:
+                q.put(None); th.join()
             barrier(); t1 = time.perf_counter()
             if rep:
                 te += maxtime(t1 - t0)
@@ -152,14 +174,14 @@ def main():
         return {"config": name, "n_gpus": world, "frames_per_step": nframes, "encode_mpix_s": mp / te, "verified": ok,
                 "codestream_bytes_per_frame": len(streams[0]) if streams else None,
                 "rank0_last_frame_ms": {"upload_run": phases[0] * 1e3, "host_tier2": phases[1] * 1e3, "gather": phases[2] * 1e3, "join": phases[3] * 1e3},
-                "sharding": "tiles of each frame over ranks (contiguous ranges), fragments gathered to rank 0 and joined"}
+                "sharding": "tiles of each frame over ranks (contiguous ranges), fragments gathered to rank 0 and joined while the next frame is encoded"}
 
     jobs = [
         ("C1", lambda: run_sequence("C1 2048x1080 8-bit RGB lossless 5/3", 1080, 2048, 3, 8, 16, True, mct=1)),
         ("C2", lambda: run_sequence("C2 4096x2160 16-bit RGBA lossless 5/3", 2160, 4096, 4, 16, 8, True, mct=1)),
         ("C3", lambda: run_sequence("C3 DCI 4K 12-bit XYZ 9/7 ICT cinema profile (PCRD rate cap)", 2160, 4096, 3, 12, 8, False,
                                     irreversible=1, mct=1, profile=L.PROFILE_CINEMA_4K)),
-        ("C4", lambda: run_tiles("C4 8192x4320 16-bit RGB lossless, 1024x1024 tiles", 4320, 8192, 3, 16, 1024, 2)),
+        ("C4", lambda: run_tiles("C4 8192x4320 16-bit RGB lossless, 1024x1024 tiles", 4320, 8192, 3, 16, 1024, args.frames8k)),
         ("C5", lambda: run_sequence("C5 4096x2160 16-bit RGB lossless sequence", 2160, 4096, 3, 16, 16, True, mct=1)),
     ]
     for key, fn in jobs:
