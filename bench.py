@@ -31,7 +31,7 @@ W, H, NC, PREC = 4096, 2160, 4, 16
 WORKLOAD = "4096x2160 16-bit RGBA lossless 5/3 (RCT, 6 resolutions, 64x64 code-blocks, 1 tile)"
 FRAMES = 16  # frames per step per GPU (one batch of the image sequence): 16 x 70.8 MB of input and 283 MB of
              # planes per frame in flight -- far beyond the 126 MB L2, so no flush is needed between steps
-TRAFFIC_L1 = 239528448  # dram__bytes_read.sum 142 346 240 + dram__bytes_write.sum 97 182 208 of one level-1 launch, from the
+TRAFFIC_L1 = 240044544  # dram__bytes_read.sum 142 349 312 + dram__bytes_write.sum 97 695 232 of one level-1 launch, from the
                         # ncu --set full capture in profiles/r1_roundtrip_full_raw.csv (part of the 141.6 MB written stays in L2)
 WORKERS = 16  # contexts (stream + buffers + host thread) the sequence keeps in flight
 
