@@ -74,31 +74,23 @@ struct MqDec {
     // st: per-context state WORD = the probability-table entry of the context's current state:
     //   qe << 16 | next-if-LPS << 8 | next-if-MPS << 1 | mps   (next-* index the table, tab = mq_state_words).
     // One shared-memory look-up per decision, a second only when the state moves.
-    // one decision with the context's state word in a register (updated in place)
-    J2K_HD inline uint32_t decode_e(uint32_t& e, const uint32_t* tab) {                // mqc.cpp:577-595
-        const uint32_t qe = e & 0xffff0000u;
+    J2K_HD inline uint32_t decode(uint32_t* st, const uint32_t* tab, uint32_t ctx) {   // mqc.cpp:577-595
+        const uint32_t e = st[ctx], qe = e & 0xffff0000u;
         uint32_t d = e & 1u;
         a -= qe;
         if (c < qe) {
-            if (a < qe) e = tab[(e >> 1) & 0x7fu];
-            else { d ^= 1u; e = tab[(e >> 8) & 0x7fu]; }
+            if (a < qe) st[ctx] = tab[(e >> 1) & 0x7fu];
+            else { d ^= 1u; st[ctx] = tab[(e >> 8) & 0x7fu]; }
             a = qe;
             renorm();
         } else {
             c -= qe;
             if ((int32_t)a >= 0) {
-                if (a < qe) { d ^= 1u; e = tab[(e >> 8) & 0x7fu]; }
-                else e = tab[(e >> 1) & 0x7fu];
+                if (a < qe) { d ^= 1u; st[ctx] = tab[(e >> 8) & 0x7fu]; }
+                else st[ctx] = tab[(e >> 1) & 0x7fu];
                 renorm();
             }
         }
-        return d;
-    }
-    J2K_HD inline uint32_t decode(uint32_t* st, const uint32_t* tab, uint32_t ctx) {
-        const uint32_t e0 = st[ctx];
-        uint32_t e = e0;
-        const uint32_t d = decode_e(e, tab);
-        if (e != e0) st[ctx] = e;
         return d;
     }
 };
@@ -318,22 +310,16 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
             } else if (passtype == 1) {
                 // magnitude refinement: significant and not coded in this plane's first pass; decisions come out in
                 // list order and are put back on their rows by the lanes afterwards
-                // (the three refinement contexts live in registers for the length of the stripe)
-                uint32_t e1 = st[CTX_MAG], e2 = st[CTX_MAG + 1], e3 = st[CTX_MAG + 2];
                 while (cols) {
                     const int x = J2K_FFSLL(cols) - 1;
                     cols &= cols - 1;
                     uint32_t list = cb.aux[x] >> 8, res = 0, k = 0;
                     do {
-                        const uint32_t code = list & 3u;
-                        uint32_t e = code == 1u ? e1 : (code == 2u ? e2 : e3);
-                        res |= mq.decode_e(e, mqtab) << k;
-                        if (code == 1u) e1 = e; else if (code == 2u) e2 = e; else e3 = e;
+                        res |= mq.decode(st, mqtab, CTX_MAG - 1 + (list & 3u)) << k;
                         ++k; list >>= 2;
                     } while (list);
                     if (res) { cb.out[x] = res; any = true; }
                 }
-                st[CTX_MAG] = e1; st[CTX_MAG + 1] = e2; st[CTX_MAG + 2] = e3;
             } else {
                 // cleanup: everything not yet significant and not visited
                 while (cols) {
