@@ -26,6 +26,7 @@ void j2kcuda_default_params(j2kcuda_params* p) {   // openjpeg.cpp:706-728
 
 int j2kcuda_t2_block_count(const j2kcuda_params* p) {
     if (!p) return -1;
+    if (const char* why = check_params(*p)) { set_error(J2KCUDA_ERR_PARAM, why); return -1; }
     CodingParams cp;
     setup_coding_params(*p, cp);
     int n = 0;
@@ -40,6 +41,7 @@ int j2kcuda_t2_block_count(const j2kcuda_params* p) {
 
 int j2kcuda_t2_block_geometry(const j2kcuda_params* p, int32_t* geo, int max_blocks) {
     if (!p || !geo) return -1;
+    if (const char* why = check_params(*p)) { set_error(J2KCUDA_ERR_PARAM, why); return -1; }
     CodingParams cp;
     setup_coding_params(*p, cp);
     int n = 0;

@@ -13,6 +13,14 @@
 
 using namespace j2k;
 
+// wait for everything queued on the stream with the calling thread asleep (cudaStreamSynchronize spins; with 16 worker
+// threads per GPU and 8 GPUs that is 128 spinning threads on the box's cores)
+static inline cudaError_t stream_wait(cudaStream_t st, cudaEvent_t ev) {
+    cudaError_t rc = cudaEventRecord(ev, st);
+    return rc != cudaSuccess ? rc : cudaEventSynchronize(ev);
+}
+
+
 #define CK(call)                                                                                   \
     do {                                                                                           \
         cudaError_t e_ = (call);                                                                   \
@@ -41,6 +49,7 @@ struct j2kcuda_decoder {
     uint8_t* d_out = nullptr; size_t d_out_cap = 0;
     uint8_t* h_out = nullptr; size_t h_out_cap = 0;                           // pinned
     cudaEvent_t ev[8];
+    cudaEvent_t ev_wait = nullptr;   // blocking-sync event: the host worker sleeps instead of spinning
     float ms[8] = {0};
     uint64_t counters[6] = {0};
     bool prepared = false, ran = false;
@@ -53,6 +62,7 @@ static void free_decoder(j2kcuda_decoder* d) {
     cudaFree(d->d_blocks); cudaFree(d->d_seg); cudaFree(d->d_jobs); cudaFree(d->d_out);
     cudaFreeHost(d->h_seg); cudaFreeHost(d->h_out);
     for (auto& e : d->ev) if (e) cudaEventDestroy(e);
+    if (d->ev_wait) cudaEventDestroy(d->ev_wait);
     if (d->st) cudaStreamDestroy(d->st);
     delete d;
 }
@@ -207,7 +217,7 @@ static int prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned 
     if (!d->h_blocks.empty()) CK(cudaMemcpyAsync(d->d_blocks, d->h_blocks.data(), d->h_blocks.size() * sizeof(T1DecBlock), cudaMemcpyHostToDevice, d->st));
     if (!all.empty()) CK(cudaMemcpyAsync(d->d_jobs, all.data(), all.size() * sizeof(DwtJob), cudaMemcpyHostToDevice, d->st));
     CK(cudaEventRecord(d->ev[1], d->st));
-    CK(cudaStreamSynchronize(d->st));          // h_blocks / all are pageable host vectors
+    CK(stream_wait(d->st, d->ev_wait));          // h_blocks / all are pageable host vectors
     d->counters[1] = nblk; d->counters[3] = (uint64_t)len;
     d->counters[4] = seg + d->h_blocks.size() * sizeof(T1DecBlock) + all.size() * sizeof(DwtJob);
     d->prepared = true; d->ran = false;
@@ -263,7 +273,7 @@ static int run(j2kcuda_decoder* d) {
         ++launches;
     }
     CK(cudaEventRecord(d->ev[5], st));
-    CK(cudaStreamSynchronize(st));
+    CK(stream_wait(st, d->ev_wait));
     CK(cudaGetLastError());
     cudaEventElapsedTime(&d->ms[1], d->ev[0], d->ev[1]);
     cudaEventElapsedTime(&d->ms[2], d->ev[2], d->ev[3]);
@@ -303,17 +313,17 @@ static int download(j2kcuda_decoder* d, const j2kcuda_plane* planes, int nplanes
         cudaGetLastError();
         if (pinned) {
             CK(cudaMemcpyAsync(planes[0].buf, d->d_out, out_bytes, cudaMemcpyDeviceToHost, d->st));
-            CK(cudaStreamSynchronize(d->st));
+            CK(stream_wait(d->st, d->ev_wait));
         } else {
             if (int rc = grow_host(d->h_out, d->h_out_cap, out_bytes)) return rc;
             CK(cudaMemcpyAsync(d->h_out, d->d_out, out_bytes, cudaMemcpyDeviceToHost, d->st));
-            CK(cudaStreamSynchronize(d->st));
+            CK(stream_wait(d->st, d->ev_wait));
             memcpy(planes[0].buf, d->h_out, out_bytes);
         }
     } else {
         if (int rc = grow_host(d->h_out, d->h_out_cap, out_bytes)) return rc;
         CK(cudaMemcpyAsync(d->h_out, d->d_out, out_bytes, cudaMemcpyDeviceToHost, d->st));
-        CK(cudaStreamSynchronize(d->st));
+        CK(stream_wait(d->st, d->ev_wait));
         for (int c = 0; c < nc; ++c) {
             const j2kcuda_plane& p = planes[c];
             const int depth = p.depth ? p.depth : cp.comps[c].prec, prec = cp.comps[c].prec, ds = sb(p.sample_type);
@@ -350,6 +360,7 @@ j2kcuda_decoder* j2kcuda_decoder_create(int device) {
     bool ok = cudaSetDevice(d->device) == cudaSuccess && device_tables_init() == nullptr &&
               cudaStreamCreateWithFlags(&d->st, cudaStreamNonBlocking) == cudaSuccess;
     for (auto& e : d->ev) ok = ok && cudaEventCreate(&e) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&d->ev_wait, cudaEventBlockingSync | cudaEventDisableTiming) == cudaSuccess;
     if (!ok) { set_error(J2KCUDA_ERR_CUDA, "decoder_create: CUDA initialisation failed"); free_decoder(d); return nullptr; }
     return d;
 }
@@ -416,7 +427,7 @@ int j2kcuda_decoder_copy_to_device(j2kcuda_decoder* d, void* d_pixels, int64_t p
     if (pitch_bytes < (int64_t)row) return set_error(J2KCUDA_ERR_PARAM, "destination pitch smaller than a decoded row");
     CK(cudaSetDevice(d->device));
     CK(cudaMemcpy2DAsync(d_pixels, (size_t)pitch_bytes, d->d_out, row, row, (size_t)d->outH, cudaMemcpyDeviceToDevice, d->st));
-    CK(cudaStreamSynchronize(d->st));
+    CK(stream_wait(d->st, d->ev_wait));
     return J2KCUDA_OK;
 }
 

@@ -15,6 +15,14 @@
 
 using namespace j2k;
 
+// wait for everything queued on the stream with the calling thread asleep (cudaStreamSynchronize spins; with 16 worker
+// threads per GPU and 8 GPUs that is 128 spinning threads on the box's cores)
+static inline cudaError_t stream_wait(cudaStream_t st, cudaEvent_t ev) {
+    cudaError_t rc = cudaEventRecord(ev, st);
+    return rc != cudaSuccess ? rc : cudaEventSynchronize(ev);
+}
+
+
 #define CK(call)                                                                                   \
     do {                                                                                           \
         cudaError_t e_ = (call);                                                                   \
@@ -61,6 +69,7 @@ struct j2kcuda_encoder {
     int row0 = 0, row1 = 0;    // image rows covered by this context's tiles (all rows unless a tile range is set)
     // timing
     cudaEvent_t ev[10];
+    cudaEvent_t ev_wait = nullptr;   // blocking-sync event: the host worker sleeps instead of spinning (many workers per core)
     float ms[8] = {0};
     uint64_t counters[6] = {0};
     bool ran = false;
@@ -75,14 +84,14 @@ static void free_encoder(j2kcuda_encoder* e) {
     cudaFree(e->d_pass_nsym); cudaFree(e->d_results); cudaFree(e->d_offsets); cudaFree(e->d_packed);
     cudaFreeHost(e->h_results); cudaFreeHost(e->h_offsets); cudaFreeHost(e->h_packed);
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
+    if (e->ev_wait) cudaEventDestroy(e->ev_wait);
     if (e->st) cudaStreamDestroy(e->st);
     delete e;
 }
 
 static int setup_encoder(j2kcuda_encoder* e) {
     const j2kcuda_params& p = e->p;
-    if (!p.width || !p.height || p.ncomp < 1 || p.ncomp > 4 || p.prec < 1 || p.prec > 16)
-        return set_error(J2KCUDA_ERR_PARAM, "unsupported image geometry (1-4 components, 1-16 bits)");
+    if (const char* why = check_params(p)) return set_error(J2KCUDA_ERR_PARAM, why);
     setup_coding_params(p, e->cp);
     const CodingParams& cp = e->cp;
     e->W = (int)p.width; e->H = (int)p.height; e->ncomp = (int)p.ncomp;
@@ -103,6 +112,7 @@ static int setup_encoder(j2kcuda_encoder* e) {
     if (const char* err = device_tables_init()) return set_error(J2KCUDA_ERR_CUDA, err);
     CK(cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking));
     for (auto& ev : e->ev) CK(cudaEventCreate(&ev));
+    CK(cudaEventCreateWithFlags(&e->ev_wait, cudaEventBlockingSync | cudaEventDisableTiming));
     const size_t plane_bytes = (size_t)e->pitch * e->H * sizeof(int32_t);
     for (int c = 0; c < e->ncomp; ++c) {
         CK(cudaMalloc(&e->planeA[c], plane_bytes));
@@ -266,7 +276,7 @@ static int upload_planes(j2kcuda_encoder* e, const j2kcuda_plane* planes, int np
             CK(cudaMemcpyAsync(e->d_pix + m.dev, m.lo, n, cudaMemcpyHostToDevice, e->st));
         } else {
             if (total > e->h_pix_cap) {
-                CK(cudaStreamSynchronize(e->st));
+                CK(stream_wait(e->st, e->ev_wait));
                 cudaFreeHost(e->h_pix); e->h_pix = nullptr; e->h_pix_cap = 0;
                 CK(cudaMallocHost(&e->h_pix, total + 256));
                 e->h_pix_cap = total;
@@ -381,7 +391,7 @@ int j2kcuda_encoder_run(j2kcuda_encoder* e) {
         CK(cudaMemcpyAsync(e->h_results, e->d_results, (size_t)e->nblocks * sizeof(T1Result), cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(e->h_offsets, e->d_offsets, ((size_t)e->nblocks + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     }
-    CK(cudaStreamSynchronize(st));
+    CK(stream_wait(st, e->ev_wait));
     CK(cudaGetLastError());
     size_t packed = e->nblocks ? e->h_offsets[e->nblocks] : 0;
     if (packed > e->h_packed_cap) {
@@ -392,7 +402,7 @@ int j2kcuda_encoder_run(j2kcuda_encoder* e) {
     }
     if (packed) CK(cudaMemcpyAsync(e->h_packed, e->d_packed, packed, cudaMemcpyDeviceToHost, st));
     CK(cudaEventRecord(e->ev[5], st));
-    CK(cudaStreamSynchronize(st));
+    CK(stream_wait(st, e->ev_wait));
     uint64_t nsym = 0;
     for (int i = 0; i < e->nblocks; ++i) {
         if (e->h_results[i].status != 0)

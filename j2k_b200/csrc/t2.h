@@ -95,6 +95,7 @@ struct EncoderHost {
     bool assemble(std::vector<EncTile>& tiles, std::vector<uint8_t>& out, std::string& err);
 };
 
+const char* check_params(const ::j2kcuda_params& p);                      // nullptr = acceptable (j2k.cpp:6640-6680)
 void setup_coding_params(const ::j2kcuda_params& p, CodingParams& cp);   // j2k.cpp:5842-6216
 void init_enc_tile(const CodingParams& cp, int tileno, EncTile& t);
 bool join_tile_streams(const CodingParams& cp, const uint8_t* const* frags, const size_t* lens, int nfrags,

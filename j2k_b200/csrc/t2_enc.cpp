@@ -16,6 +16,28 @@ namespace j2k {
 static const char* kCommentGrok = "Created by Grok     version 2.1.1";
 static const char* kCommentOpj25 = "Created by OpenJPEG version 2.5.4";
 
+// What the reference refuses before it encodes (opj_compress parameter checks and opj_j2k_encoding_validation,
+// j2k.cpp:6640-6680), plus the limits of this library.  nullptr = fine.
+const char* check_params(const ::j2kcuda_params& p) {
+    if (!p.width || !p.height) return "empty image";
+    if (p.ncomp < 1 || p.ncomp > 4) return "unsupported image geometry (1-4 components, 1-16 bits)";
+    if (p.prec < 1 || p.prec > 16) return "unsupported image geometry (1-4 components, 1-16 bits)";
+    uint32_t numres = p.numresolution ? p.numresolution : 6;
+    const bool cinema = p.profile == J2KCUDA_PROFILE_CINEMA_2K || p.profile == J2KCUDA_PROFILE_CINEMA_4K;
+    if (cinema) numres = p.profile == J2KCUDA_PROFILE_CINEMA_2K ? std::min(numres, 6u) : std::min(std::max(numres, 1u), 7u);
+    if (numres > 33) return "Invalid number of resolutions : not in range [1,33]";
+    const bool tiled = p.tile_w && p.tile_h && !cinema;
+    const uint64_t tdx = tiled ? p.tile_w : p.width, tdy = tiled ? p.tile_h : p.height;
+    if (tdx < ((uint64_t)1 << (numres - 1)) || tdy < ((uint64_t)1 << (numres - 1)))
+        return "Number of resolutions is too high in comparison to the size of tiles";
+    const uint32_t cw = p.cblk_w ? p.cblk_w : 64, ch = p.cblk_h ? p.cblk_h : 64;
+    if (cw < 4 || ch < 4 || cw > 1024 || ch > 1024 || (cw & (cw - 1)) || (ch & (ch - 1)) || (uint64_t)cw * ch > 4096)
+        return "code-block size must be a power of two between 4 and 1024 with at most 4096 samples";
+    if (p.numlayers > 100) return "too many layers";
+    if (p.prog_order > J2KCUDA_CPRL) return "unknown progression order";
+    return nullptr;
+}
+
 void setup_coding_params(const ::j2kcuda_params& p, CodingParams& cp) {
     cp = CodingParams();
     cp.x0 = cp.y0 = 0; cp.x1 = p.width; cp.y1 = p.height;

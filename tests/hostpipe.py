@@ -17,8 +17,9 @@ def block_list(params):
     return geo
 
 
-def oracle_tile_stages(planes, prec, sgnd, params):
-    """planes: list of int32 (h,w) unsigned samples of ONE tile.  Returns DWT coefficient planes."""
+def oracle_tile_stages(planes, prec, sgnd, params, x0=0, y0=0):
+    """planes: list of int32 (h,w) unsigned samples of ONE tile whose top-left sample is (x0, y0) of the image (the parity
+    of the origin at every level decides which samples are low-pass, dwt.cpp:420-506).  Returns DWT coefficient planes."""
     irreversible = int(params.irreversible)
     numres = int(params.numresolution) or 6
     shift = 0 if sgnd else 1 << (prec - 1)
@@ -27,7 +28,7 @@ def oracle_tile_stages(planes, prec, sgnd, params):
         p = [x * 2048 for x in p]          # tcd.cpp:1659-1696: 11 fractional bits
     if params.mct and len(p) >= 3:
         p[:3] = orc.mct(p[0], p[1], p[2], real=bool(irreversible))
-    return [orc.dwt(x, numres, real=bool(irreversible)) for x in p]
+    return [orc.dwt(x, numres, real=bool(irreversible), x0=x0, y0=y0) for x in p]
 
 
 def encode(planes, prec, params, sgnd=0):
@@ -47,7 +48,7 @@ def encode(planes, prec, params, sgnd=0):
         if tile not in coeffs:
             tx, ty = tile % ntx, tile // ntx
             sub = [pl[ty * th:(ty + 1) * th, tx * tw:(tx + 1) * tw] for pl in planes]
-            coeffs[tile] = oracle_tile_stages(sub, prec, sgnd, params)
+            coeffs[tile] = oracle_tile_stages(sub, prec, sgnd, params, x0=tx * tw, y0=ty * th)
         blk = coeffs[tile][comp][py:py + bh, px:px + bw]
         if bw == 0 or bh == 0:
             r = dict(data=b"", numbps=0, npasses=0, rates=[], nmsedec=[])

@@ -1,0 +1,127 @@
+"""Edge cases of the codec path, against the compiled reference: degenerate and ragged geometries (1x1, single row /
+column, smaller than 2^levels, widths that are not a multiple of the 16-byte vector), empty content (all-zero planes:
+every code-block absent from the packets), saturated content, non-square code-blocks, two components, odd precisions,
+ragged tiles; and the error behaviour of the C ABI (bad parameters, truncated and corrupt streams: a status and a
+message, never a crash).  CPU: host Tier-2 + oracle stages.  GPU: the CUDA path through the C ABI."""
+import ctypes as C
+import numpy as np
+import pytest
+from j2k_b200 import _lib as L
+from j2k_b200.frames import make_frame
+import hostpipe
+import refgrok
+
+needs_ref = pytest.mark.skipif(not refgrok.available(), reason="oracle/_ref not built")
+
+GEOMETRIES = [  # h, w, ncomp, prec, numres, cblk_w, cblk_h, tile
+    (1, 1, 1, 8, 1, 64, 64, 0), (1, 1, 3, 8, 6, 64, 64, 0), (1, 37, 1, 8, 6, 64, 64, 0), (41, 1, 1, 16, 6, 64, 64, 0),
+    (2, 2, 3, 8, 3, 64, 64, 0), (3, 5, 3, 12, 6, 64, 64, 0), (5, 7, 4, 16, 6, 32, 32, 0), (17, 130, 3, 8, 5, 128, 32, 0),
+    (70, 33, 2, 10, 4, 16, 64, 0), (65, 129, 3, 8, 2, 4, 4, 0), (50, 75, 3, 9, 4, 64, 64, 32), (33, 100, 1, 1, 3, 64, 64, 0),
+    (40, 100, 3, 16, 6, 64, 64, 48),
+]
+
+
+def content(kind, h, w, nc, prec):
+    if kind == "zero":
+        return np.zeros((h, w, nc), np.uint16 if prec > 8 else np.uint8)
+    if kind == "max":
+        return np.full((h, w, nc), (1 << prec) - 1, np.uint16 if prec > 8 else np.uint8)
+    if kind == "mid":                       # exactly the DC level: every coefficient zero after the level shift
+        return np.full((h, w, nc), 1 << (prec - 1), np.uint16 if prec > 8 else np.uint8)
+    return make_frame(h, w, nc, prec, kind, seed=11)
+
+
+def ref_encode(img, prec, numres, cw, ch, tile, mct):
+    """-> bytes, or None when the reference refuses the parameters (e.g. more resolutions than the tile has samples for)"""
+    planes = [img[..., c].astype(np.int32) for c in range(img.shape[2])]
+    try:
+        return refgrok.encode(planes, prec, mct=mct, numresolution=numres, cblk=(cw, ch), tile=(tile, tile))
+    except RuntimeError:
+        return None
+
+
+@needs_ref
+@pytest.mark.parametrize("h,w,nc,prec,numres,cw,ch,tile", GEOMETRIES)
+@pytest.mark.parametrize("kind", ["noise", "zero"])
+def test_host_tier2_on_degenerate_geometries(h, w, nc, prec, numres, cw, ch, tile, kind):
+    img = content(kind, h, w, nc, prec)
+    mct = 1 if nc >= 3 else 0
+    p = L.default_params(width=w, height=h, ncomp=nc, prec=prec, mct=mct, numresolution=numres, cblk_w=cw, cblk_h=ch, tile_w=tile, tile_h=tile)
+    ref = ref_encode(img, prec, numres, cw, ch, tile, mct)
+    if ref is None:
+        if numres > 1 and min(tile or w, tile or h) < (1 << (numres - 1)):
+            # what the reference refuses, the library refuses (with the reference's message, j2k.cpp:6664-6672)
+            assert L.lib().j2kcuda_t2_block_count(C.byref(p)) < 0
+            assert "resolutions" in L.last_error()
+            return
+        pytest.skip("the reference's tile buffer (0.1625 x raw size, j2k.cpp:4451-4462) overflows on this input")
+    ours = hostpipe.encode([img[..., c].astype(np.int32) for c in range(nc)], prec, p)
+    assert ours == ref
+
+
+@pytest.mark.gpu
+@needs_ref
+@pytest.mark.parametrize("h,w,nc,prec,numres,cw,ch,tile", GEOMETRIES)
+@pytest.mark.parametrize("kind", ["noise", "zero", "max", "mid"])
+def test_cuda_path_on_degenerate_geometries(h, w, nc, prec, numres, cw, ch, tile, kind):
+    import j2k
+    img = content(kind, h, w, nc, prec)
+    mct = 1 if nc >= 3 else 0
+    ref = ref_encode(img, prec, numres, cw, ch, tile, mct)
+    if ref is None and numres > 1 and min(tile or w, tile or h) < (1 << (numres - 1)):
+        p = L.default_params(width=w, height=h, ncomp=nc, prec=prec, mct=mct, numresolution=numres, cblk_w=cw, cblk_h=ch, tile_w=tile, tile_h=tile)
+        L.lib().j2kcuda_encoder_create.restype = C.c_void_p
+        assert not L.lib().j2kcuda_encoder_create(C.byref(p))
+        return
+    ours = j2k.encode(img, prec, mct=mct, numresolution=numres, cblk_w=cw, cblk_h=ch, tile_w=tile, tile_h=tile)
+    if ref is not None:
+        assert ours == ref
+    else:                                   # the reference's encoder overflows its own tile buffer here; its decoder is the arbiter
+        assert all(np.array_equal(a, img[..., c]) for c, a in enumerate(refgrok.decode(ours)))
+    assert np.array_equal(j2k.decode(ours), img)
+    for reduce in (1, 2):
+        if reduce < numres:
+            want = refgrok.decode(ours, reduce=reduce)
+            got = j2k.decode(ours, reduce=reduce)
+            assert all(np.array_equal(got[..., c], want[c]) for c in range(nc))
+
+
+def test_bad_parameters_are_refused_with_a_message():
+    lib = L.lib()
+    lib.j2kcuda_encoder_create.restype = C.c_void_p
+    for kw in (dict(width=0, height=4, ncomp=1, prec=8), dict(width=4, height=4, ncomp=0, prec=8), dict(width=4, height=4, ncomp=5, prec=8),
+               dict(width=4, height=4, ncomp=1, prec=0), dict(width=4, height=4, ncomp=1, prec=17),
+               dict(width=4, height=4, ncomp=1, prec=8, cblk_w=48), dict(width=4, height=4, ncomp=1, prec=8, cblk_w=1024, cblk_h=1024),
+               dict(width=4, height=4, ncomp=1, prec=8, numresolution=40)):
+        p = L.default_params(**kw)
+        assert lib.j2kcuda_t2_block_count(C.byref(p)) < 0 or not lib.j2kcuda_encoder_create(C.byref(p)), kw
+    assert lib.j2kcuda_probe(None, C.c_size_t(0), None) == L.ERR_PARAM
+    info = L.Info()
+    assert lib.j2kcuda_probe(b"", C.c_size_t(0), C.byref(info)) in (L.ERR_STREAM, L.ERR_PARAM)
+
+
+@needs_ref
+def test_truncated_and_corrupt_streams_are_rejected_by_the_parser():
+    img = make_frame(40, 60, 3, 8, "smooth", seed=1)
+    cs = ref_encode(img, 8, 4, 64, 64, 0, 1)
+    lib = L.lib()
+    info = C.POINTER(C.c_int32)(); nb = C.c_int(0); seg = C.POINTER(C.c_uint8)(); n = C.c_size_t(0)
+
+    def parse(data):
+        rc = lib.j2kcuda_t2_parse(data, C.c_size_t(len(data)), 0, C.byref(info), C.byref(nb), C.byref(seg), C.byref(n))
+        if rc == 0:
+            lib.j2kcuda_free(info); lib.j2kcuda_free(seg)
+        return rc
+
+    assert parse(cs) == 0
+    rng = np.random.default_rng(0)
+    for cut in (2, 10, 40, 60, 100, len(cs) // 2, len(cs) - 3):
+        rc = parse(cs[:cut])
+        assert rc in (0, L.ERR_STREAM, L.ERR_UNSUPPORTED)            # the reference also accepts a stream cut inside the last packets
+        if cut < 100:
+            assert rc != 0 and L.last_error()
+    for _ in range(200):                                             # random byte damage in the headers: a status, never a crash
+        bad = bytearray(cs)
+        for k in rng.integers(2, 120, size=3):
+            bad[int(k)] = int(rng.integers(0, 256))
+        assert parse(bytes(bad)) in (0, L.ERR_STREAM, L.ERR_UNSUPPORTED, L.ERR_PARAM)
