@@ -15,7 +15,7 @@ needs_ref = pytest.mark.skipif(not refgrok.available(), reason="oracle/_ref not 
 
 GEOMETRIES = [  # h, w, ncomp, prec, numres, cblk_w, cblk_h, tile
     (1, 1, 1, 8, 1, 64, 64, 0), (1, 1, 3, 8, 6, 64, 64, 0), (1, 37, 1, 8, 6, 64, 64, 0), (41, 1, 1, 16, 6, 64, 64, 0),
-    (2, 2, 3, 8, 3, 64, 64, 0), (3, 5, 3, 12, 6, 64, 64, 0), (5, 7, 4, 16, 6, 32, 32, 0), (17, 130, 3, 8, 5, 128, 32, 0),
+    (2, 2, 3, 8, 3, 64, 64, 0), (3, 5, 3, 12, 6, 64, 64, 0), (5, 7, 4, 16, 6, 32, 32, 0), (17, 130, 3, 8, 5, 64, 16, 0),
     (70, 33, 2, 10, 4, 16, 64, 0), (65, 129, 3, 8, 2, 4, 4, 0), (50, 75, 3, 9, 4, 64, 64, 32), (33, 100, 1, 1, 3, 64, 64, 0),
     (40, 100, 3, 16, 6, 64, 64, 48),
 ]
@@ -84,6 +84,17 @@ def test_cuda_path_on_degenerate_geometries(h, w, nc, prec, numres, cw, ch, tile
             want = refgrok.decode(ours, reduce=reduce)
             got = j2k.decode(ours, reduce=reduce)
             assert all(np.array_equal(got[..., c], want[c]) for c in range(nc))
+
+
+@pytest.mark.gpu
+def test_code_blocks_wider_or_taller_than_64_are_refused_not_miscoded():
+    """the reference allows up to 1024 x 4; the CUDA Tier-1 keeps a block's rows as 64-bit masks"""
+    lib = L.lib()
+    lib.j2kcuda_encoder_create.restype = C.c_void_p
+    for cw, ch in ((128, 32), (32, 128), (1024, 4)):
+        p = L.default_params(width=256, height=256, ncomp=1, prec=8, cblk_w=cw, cblk_h=ch)
+        assert not lib.j2kcuda_encoder_create(C.byref(p))
+        assert "64x64" in L.last_error()
 
 
 def test_bad_parameters_are_refused_with_a_message():
