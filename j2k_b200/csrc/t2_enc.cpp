@@ -229,6 +229,7 @@ static uint64_t encode_packet(const CodingParams& cp, EncTile& t, const PacketId
     if (!layno) {
         for (int b = 0; b < res.numbands; ++b) {
             const BandGeo& band = res.bands[b];
+            if (band.r.w() <= 0 || band.r.h() <= 0) continue;          // see the note above encode_packet
             const PrecGeo& prc = band.precs[precno];
             int ti = tree_index(cp, t, compno, resno, b, precno);
             t.incl[ti].reset(); t.imsb[ti].reset();
@@ -242,6 +243,7 @@ static uint64_t encode_packet(const CodingParams& cp, EncTile& t, const PacketId
     BitWriter bio; bio.out = out;
     bio.putbit(1);
     for (int b = 0; b < res.numbands; ++b) {
+        if (res.bands[b].r.w() <= 0 || res.bands[b].r.h() <= 0) continue;
         const PrecGeo& prc = res.bands[b].precs[precno];
         int ti = tree_index(cp, t, compno, resno, b, precno);
         int nb = prc.cw * prc.ch;
@@ -272,6 +274,7 @@ static uint64_t encode_packet(const CodingParams& cp, EncTile& t, const PacketId
         nbytes += 2;
     }
     for (int b = 0; b < res.numbands; ++b) {
+        if (res.bands[b].r.w() <= 0 || res.bands[b].r.h() <= 0) continue;
         const PrecGeo& prc = res.bands[b].precs[precno];
         for (int k = 0; k < prc.cw * prc.ch; ++k) {
             EncBlock& cblk = t.blocks[prc.first_cblk + k];
