@@ -3,6 +3,7 @@
 // Mirrors opj_tcd_decode_tile (ext/grok/src/lib/openjp2/tcd.cpp:1106-1137).  No CPU pixel path.
 #include "../../include/j2kcuda.h"
 #include "common.h"
+#include <thread>
 #include "device.h"
 #include "t2.h"
 #include <algorithm>
@@ -316,9 +317,29 @@ static int download(j2kcuda_decoder* d, const j2kcuda_plane* planes, int nplanes
             CK(stream_wait(d->st, d->ev_wait));
         } else {
             if (int rc = grow_host(d->h_out, d->h_out_cap, out_bytes)) return rc;
-            CK(cudaMemcpyAsync(d->h_out, d->d_out, out_bytes, cudaMemcpyDeviceToHost, d->st));
+            // pageable destination: D2H into the page-locked buffer in quarters, each quarter copied out by its own
+            // thread as soon as its DMA has finished
+            const int parts = out_bytes >= (32u << 20) ? 4 : 1;
+            cudaEvent_t evp[4] = {nullptr, nullptr, nullptr, nullptr};
+            size_t cut[5];
+            for (int i = 0; i <= parts; ++i) cut[i] = (out_bytes * (size_t)i / (size_t)parts) & ~(size_t)255;
+            cut[parts] = out_bytes;
+            bool ok = true;
+            for (int i = 0; i < parts; ++i) {
+                ok = ok && cudaMemcpyAsync(d->h_out + cut[i], d->d_out + cut[i], cut[i + 1] - cut[i], cudaMemcpyDeviceToHost, d->st) == cudaSuccess;
+                ok = ok && cudaEventCreateWithFlags(&evp[i], cudaEventBlockingSync | cudaEventDisableTiming) == cudaSuccess;
+                ok = ok && cudaEventRecord(evp[i], d->st) == cudaSuccess;
+            }
+            std::vector<std::thread> th;
+            auto work = [&](int i) {
+                if (evp[i] && cudaEventSynchronize(evp[i]) == cudaSuccess) memcpy((uint8_t*)planes[0].buf + cut[i], d->h_out + cut[i], cut[i + 1] - cut[i]);
+            };
+            for (int i = 1; i < parts && ok; ++i) th.emplace_back(work, i);
+            if (ok) work(0);
+            for (auto& x : th) x.join();
+            for (int i = 0; i < parts; ++i) if (evp[i]) cudaEventDestroy(evp[i]);
+            if (!ok) { CK(cudaGetLastError()); return set_error(J2KCUDA_ERR_CUDA, "download failed"); }
             CK(stream_wait(d->st, d->ev_wait));
-            memcpy(planes[0].buf, d->h_out, out_bytes);
         }
     } else {
         if (int rc = grow_host(d->h_out, d->h_out_cap, out_bytes)) return rc;
