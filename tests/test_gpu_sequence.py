@@ -109,3 +109,35 @@ def test_sequence_reports_worker_errors():
     assert rc == L.ERR_STREAM, (rc, L.last_error())
     assert L.last_error()
     lib.j2kcuda_sequence_destroy(seq)
+
+
+def test_one_shot_calls_are_reentrant():
+    """The plug-in's codec objects are process-wide singletons and After Effects calls them from several render threads
+    (threading): concurrent j2kcuda_encode / j2kcuda_decode calls with different parameters must not disturb
+    each other.  Every thread's codestream must equal the one the same call gives alone."""
+    import threading
+    jobs = [(96, 128, 3, 8, dict(mct=1)), (130, 200, 4, 16, dict(mct=1)), (75, 133, 1, 8, dict(numresolution=4, cblk_w=32, cblk_h=32)),
+            (100, 160, 3, 12, dict(irreversible=1, mct=1, rates=[10.0])), (200, 340, 3, 16, dict(mct=1, tile_w=64, tile_h=64)),
+            (64, 64, 3, 8, dict(mct=1, prog_order=3))]
+    imgs = [make_frame(h, w, nc, prec, "smooth" if i % 2 else "noise", seed=i) for i, (h, w, nc, prec, kw) in enumerate(jobs)]
+    alone = [j2k.encode(img, job[3], **job[4]) for img, job in zip(imgs, jobs)]
+    decoded_alone = [j2k.decode(cs) for cs in alone]
+    errors = []
+
+    def worker(i):
+        try:
+            for _ in range(4):
+                cs = j2k.encode(imgs[i], jobs[i][3], **jobs[i][4])
+                if cs != alone[i]:
+                    errors.append("thread %d: codestream differs" % i)
+                if not np.array_equal(j2k.decode(cs), decoded_alone[i]):
+                    errors.append("thread %d: decoded pixels differ" % i)
+        except AssertionError as e:
+            errors.append("thread %d: %s" % (i, e))
+
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(len(jobs))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
