@@ -626,7 +626,7 @@ bool EncoderHost::assemble(std::vector<EncTile>& tiles, std::vector<uint8_t>& ou
     for (int i = 0; i < nt; ++i) {
         if (!cp.tile_in_range(i)) continue;
         EncTile& t = tiles[i];
-        double rates[16];
+        double rates[16] = {0};
         double offset = (cp.tp_on ? (double)(float)((parts[i].size() - 1) * 14) : 0.0) / cp.numlayers;
         double bits_empty = 8.0 * cp.comps[0].dx * cp.comps[0].dy;
         double size_pixel = (double)cp.ncomp * cp.comps[0].prec;
