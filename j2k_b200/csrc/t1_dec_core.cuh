@@ -151,6 +151,7 @@ J2K_HD inline uint8_t sc_entry(const uint8_t* sc, int i) {
 //   aux[x]  nibbles: bits 0-3 samples to code in this pass (membership / validity), 4-7 refined
 //   out[x]  nibbles: 0-3 newly significant, 4-7 negative, 8-11 visited, 12-15 decoded magnitude bit
 struct ColBuf {
+    uint32_t gwin[64];        // sign window of column x, same layout as win (significance and cleanup passes)
     uint32_t win[64];
     uint32_t aux[64];
     uint32_t out[64];
@@ -242,6 +243,12 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
             // ---- column-major set-up, two columns per lane ----
             for (int x = lane; x < 64; x += nlanes) {
                 cb.win[x] = pack_win(S, x);
+                if (passtype != 1) {
+                    u64 G[6];
+#pragma unroll
+                    for (int q = 0; q < 6; ++q) G[q] = R.sgn[ib + q];
+                    cb.gwin[x] = pack_win(G, x);
+                }
                 uint32_t a = nibble(memb, x);
                 if (passtype == 1) {
                     // magnitude refinement contexts depend on nothing decoded in this pass: the column's list of
@@ -286,10 +293,7 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
                         const uint32_t s9 = (win >> (3 * r)) & 0x1ffu;
                         if (!mq.decode(st, mqtab, zc[s9 & 0x1efu])) continue;
                         if (!have_g) {
-                            u64 G[6];
-#pragma unroll
-                            for (int q = 0; q < 6; ++q) G[q] = R.sgn[ib + q];
-                            gwin = pack_win(G, x);
+                            gwin = cb.gwin[x];
                             if (x == carry_x + 1) gwin |= carry_g;
                             have_g = true;
                         }
@@ -348,10 +352,7 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
                         if (partial) partial = false;                  // the sample that ended the run is significant
                         else if (!mq.decode(st, mqtab, zc[s9 & 0x1efu])) continue;
                         if (!have_g) {
-                            u64 G[6];
-#pragma unroll
-                            for (int q = 0; q < 6; ++q) G[q] = R.sgn[ib + q];
-                            gwin = pack_win(G, x);
+                            gwin = cb.gwin[x];
                             if (x == carry_x + 1) gwin |= carry_g;
                             have_g = true;
                         }
