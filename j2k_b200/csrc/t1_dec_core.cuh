@@ -10,6 +10,7 @@
 #endif
 #if defined(__CUDA_ARCH__)
 #define J2K_FFSLL(v) __ffsll((long long)(v))
+#define J2K_FFS(v) __ffs((int)(v))
 #define J2K_CLZ(v) __clz((int)(v))
 #define J2K_SYNCWARP() __syncwarp()
 #define J2K_FMUL(a, b) __fmul_rn((a), (b))
@@ -17,6 +18,7 @@
 #else
 #define J2K_NOINLINE
 #define J2K_FFSLL(v) __builtin_ffsll((long long)(v))
+#define J2K_FFS(v) __builtin_ffs((int)(v))
 #define J2K_CLZ(v) __builtin_clz((unsigned)(v))
 #define J2K_SYNCWARP() ((void)0)
 #define J2K_FMUL(a, b) ((a) * (b))
@@ -182,7 +184,9 @@ J2K_HD inline uint32_t mr_rows(uint32_t res, uint32_t mem4) {
 }
 // nibble -> the window bits of rows 1..4 at column offset 0 (bits 3, 6, 9, 12)
 J2K_HD inline uint32_t spread4(uint32_t n) {
-    return ((n & 1u) << 3) | ((n & 2u) << 5) | ((n & 4u) << 7) | ((n & 8u) << 9);
+    n = (n | (n << 4)) & 0xc3u;            // bits 0 1 . . . . 2 3
+    n = (n | (n << 2)) & 0x249u;           // bits 0, 3, 6, 9
+    return n << 3;
 }
 
 // Decode one code-block.  Called by all `nlanes` lanes of a warp with identical arguments except `lane`;
@@ -271,10 +275,16 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
             int carry_x = -2;
             uint32_t carry_s = 0, carry_g = 0;
             if (passtype == 0) {
-                u64 active = cols, donec = 0;
-                while (u64 rem = active & ~donec) {
-                    const int x = J2K_FFSLL(rem) - 1;
-                    donec |= 1ull << x;
+                // the 64 columns as two 32-bit halves: find-first-set and the mask updates are single instructions
+                uint32_t pend = 0;
+#pragma unroll 1
+                for (int hh = 0; hh < 2; ++hh) {
+                const uint32_t cm32 = (uint32_t)(colmask >> (32 * hh));
+                uint32_t active = ((uint32_t)(cols >> (32 * hh)) | pend) & cm32, donec = 0, rem;
+                pend = 0;
+                while ((rem = active & ~donec) != 0) {
+                    const int xl = J2K_FFS(rem) - 1, x = 32 * hh + xl;
+                    donec |= 1u << xl;
                     uint32_t win = cb.win[x];
                     if (x == carry_x + 1) win |= carry_s;
                     const uint32_t mem4 = cb.aux[x];
@@ -294,7 +304,7 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
                         if (!mq.decode(st, mqtab, zc[s9 & 0x1efu])) continue;
                         if (!have_g) {
                             gwin = cb.gwin[x];
-                            if (x == carry_x + 1) gwin |= carry_g;
+                            if (x == carry_x + 1) gwin |= spread4(carry_g);
                             have_g = true;
                         }
                         const uint32_t e = sc[sc_index(s9, (gwin >> (3 * r)) & 0x1ffu)];
@@ -307,16 +317,21 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
                     }
                     if (vis4) { cb.out[x] = new4 | (neg4 << 4) | (vis4 << 8); any = true; }
                     if (new4) {
-                        carry_x = x; carry_s = spread4(new4); carry_g = spread4(neg4);
-                        active |= (2ull << x) & colmask;               // the next column may now hold candidates
+                        carry_x = x; carry_s = spread4(new4); carry_g = neg4;
+                        active |= (2u << xl) & cm32;                   // the next column may now hold candidates
+                        if (xl == 31) pend = 1u;
                     }
+                }
                 }
             } else if (passtype == 1) {
                 // magnitude refinement: significant and not coded in this plane's first pass; decisions come out in
                 // list order and are put back on their rows by the lanes afterwards
-                while (cols) {
-                    const int x = J2K_FFSLL(cols) - 1;
-                    cols &= cols - 1;
+#pragma unroll 1
+                for (int hh = 0; hh < 2; ++hh) {
+                uint32_t c32 = (uint32_t)(cols >> (32 * hh));
+                while (c32) {
+                    const int x = 32 * hh + J2K_FFS(c32) - 1;
+                    c32 &= c32 - 1;
                     uint32_t list = cb.aux[x] >> 8, res = 0, k = 0;
                     do {
                         res |= mq.decode(st, mqtab, CTX_MAG - 1 + (list & 3u)) << k;
@@ -324,11 +339,16 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
                     } while (list);
                     if (res) { cb.out[x] = res; any = true; }
                 }
+                }
             } else {
                 // cleanup: everything not yet significant and not visited
-                while (cols) {
-                    const int x = J2K_FFSLL(cols) - 1;
-                    cols &= cols - 1;
+#pragma unroll 1
+                for (int hh = 0; hh < 2; ++hh) {
+                uint32_t c32 = (uint32_t)(cols >> (32 * hh));
+                const uint32_t mall32 = (uint32_t)(memall >> (32 * hh));
+                while (c32) {
+                    const int xl = J2K_FFS(c32) - 1, x = 32 * hh + xl;
+                    c32 &= c32 - 1;
                     uint32_t win = cb.win[x];
                     if (x == carry_x + 1) win |= carry_s;
                     uint32_t gwin = 0;
@@ -336,7 +356,7 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
                     const uint32_t mem4 = cb.aux[x];
                     int rstart = 0;
                     bool partial = false;
-                    if (((memall >> x) & 1ull) && win == 0) {
+                    if (((mall32 >> xl) & 1u) && win == 0) {
                         // run-length mode: the whole column and its neighbourhood are insignificant
                         if (!mq.decode(st, mqtab, CTX_AGG)) continue;
                         rstart = (int)mq.decode(st, mqtab, CTX_UNI);
@@ -353,7 +373,7 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
                         else if (!mq.decode(st, mqtab, zc[s9 & 0x1efu])) continue;
                         if (!have_g) {
                             gwin = cb.gwin[x];
-                            if (x == carry_x + 1) gwin |= carry_g;
+                            if (x == carry_x + 1) gwin |= spread4(carry_g);
                             have_g = true;
                         }
                         const uint32_t e = sc[sc_index(s9, (gwin >> (3 * r)) & 0x1ffu)];
@@ -364,8 +384,9 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
                     }
                     if (new4) {
                         cb.out[x] = new4 | (neg4 << 4); any = true;
-                        carry_x = x; carry_s = spread4(new4); carry_g = spread4(neg4);
+                        carry_x = x; carry_s = spread4(new4); carry_g = neg4;
                     }
+                }
                 }
             }
             J2K_SYNCWARP();
