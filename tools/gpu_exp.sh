@@ -1,0 +1,21 @@
+#!/bin/bash
+# One parametrised GPU experiment script (run through gpurun): tools/gpu_exp.sh <what> ...; results under gpurun_out/.
+mkdir -p gpurun_out
+what=${1:-tests}
+case $what in
+tests)   python -m pytest tests -m gpu -x -q 2>&1 | tail -15 | tee gpurun_out/tests.log ;;
+decsweep)
+  : > gpurun_out/decsweep.log
+  [ -z "$NOV1" ] && J2KCUDA_DEC_IMPL=0 python tools/dec_bench.py --tag v1 >> gpurun_out/decsweep.log 2>&1
+  for cfg in ${CFGS:-4_6 8_6 16_8 32_8}; do
+    a=${cfg%_*}; b=${cfg#*_}
+    J2KCUDA_DEC_LPB=$a J2KCUDA_DEC_WARPS=$b timeout 300 python tools/dec_bench.py --tag multi >> gpurun_out/decsweep.log 2>&1
+  done
+  cat gpurun_out/decsweep.log ;;
+decprof)   # ncu full capture of the Tier-1 decode kernel of one 4K frame: tools/gpu_exp.sh decprof <name> [env assignments...]
+  name=${2:-dec}; shift 2
+  env "$@" python tools/dec_bench.py --frames 1 --alone-only --tag $name > gpurun_out/${name}_plain.log 2>&1 &&
+  env "$@" ncu --set full --clock-control none --import-source on -k regex:k_t1_decode -s 2 -c 1 -f -o gpurun_out/$name \
+      python tools/dec_bench.py --frames 1 --alone-only --tag $name > gpurun_out/${name}_ncu.log 2>&1
+  cat gpurun_out/${name}_plain.log; tail -3 gpurun_out/${name}_ncu.log ;;
+esac
