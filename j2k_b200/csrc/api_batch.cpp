@@ -70,7 +70,7 @@ int run_workers(int nw, int nframes, F fn) {
 
 extern "C" {
 
-j2kcuda_sequence* j2kcuda_sequence_create(const j2kcuda_params* p, int device, int nworkers) {
+j2kcuda_sequence* j2kcuda_sequence_create(const j2kcuda_params* p, int device, int nworkers) { try {
     if (nworkers < 1) nworkers = 4;
     if (nworkers > 16) nworkers = 16;
     j2kcuda_sequence* s = new j2kcuda_sequence();
@@ -83,7 +83,7 @@ j2kcuda_sequence* j2kcuda_sequence_create(const j2kcuda_params* p, int device, i
         else s->device = p->device;
     }
     return s;
-}
+} catch (...) { set_error(J2KCUDA_ERR_NOMEM, "j2kcuda_sequence_create: out of memory or internal error"); return nullptr; } }
 
 void j2kcuda_sequence_destroy(j2kcuda_sequence* s) {
     if (!s) return;
@@ -93,7 +93,7 @@ void j2kcuda_sequence_destroy(j2kcuda_sequence* s) {
 }
 
 int j2kcuda_sequence_encode(j2kcuda_sequence* s, const j2kcuda_plane* const* frames, int nframes, int nplanes,
-                            unsigned flags, uint8_t** outs, size_t* out_lens) {
+                            unsigned flags, uint8_t** outs, size_t* out_lens) { return j2k::guarded([&]() -> int {
     if (!s || !frames || !outs || !out_lens) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     if (!s->have_params) return set_error(J2KCUDA_ERR_PARAM, "sequence was created without encoder parameters");
     if (nframes <= 0) return J2KCUDA_OK;
@@ -124,10 +124,10 @@ int j2kcuda_sequence_encode(j2kcuda_sequence* s, const j2kcuda_plane* const* fra
         }
         return rc;
     });
-}
+}); }
 
 int j2kcuda_sequence_decode(j2kcuda_sequence* s, const uint8_t* const* streams, const size_t* lens, int nframes,
-                            unsigned reduce, const j2kcuda_plane* const* frames, int nplanes, unsigned flags) {
+                            unsigned reduce, const j2kcuda_plane* const* frames, int nplanes, unsigned flags) { return j2k::guarded([&]() -> int {
     if (!s || !streams || !lens || !frames) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     if (nframes <= 0) return J2KCUDA_OK;
     const int nw = s->nworkers < nframes ? s->nworkers : nframes;
@@ -154,10 +154,10 @@ int j2kcuda_sequence_decode(j2kcuda_sequence* s, const uint8_t* const* streams, 
         }
         return rc;
     });
-}
+}); }
 
 int j2kcuda_sequence_stats(j2kcuda_sequence* s, double* enc_ms, uint64_t* enc_cnt, double* dec_ms, uint64_t* dec_cnt,
-                           uint64_t* frames, int reset) {
+                           uint64_t* frames, int reset) { return j2k::guarded([&]() -> int {
     if (!s) return set_error(J2KCUDA_ERR_PARAM, "null sequence");
     std::lock_guard<std::mutex> g(s->mu);
     for (int k = 0; k < 8; ++k) { if (enc_ms) enc_ms[k] = s->enc_ms[k]; if (dec_ms) dec_ms[k] = s->dec_ms[k]; }
@@ -169,24 +169,24 @@ int j2kcuda_sequence_stats(j2kcuda_sequence* s, double* enc_ms, uint64_t* enc_cn
         s->enc_frames = s->dec_frames = 0;
     }
     return J2KCUDA_OK;
-}
+}); }
 
 int j2kcuda_encode_batch(const j2kcuda_params* p, const j2kcuda_plane* const* frames, int nframes, int nplanes,
-                         uint8_t** outs, size_t* out_lens) {
+                         uint8_t** outs, size_t* out_lens) { return j2k::guarded([&]() -> int {
     if (!p || !frames || !outs || !out_lens) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     j2kcuda_sequence* s = j2kcuda_sequence_create(p, p->device, 0);
     int rc = j2kcuda_sequence_encode(s, frames, nframes, nplanes, 0, outs, out_lens);
     j2kcuda_sequence_destroy(s);
     return rc;
-}
+}); }
 
 int j2kcuda_decode_batch(const uint8_t* const* streams, const size_t* lens, int nframes, unsigned reduce,
-                         const j2kcuda_plane* const* frames, int nplanes) {
+                         const j2kcuda_plane* const* frames, int nplanes) { return j2k::guarded([&]() -> int {
     if (!streams || !lens || !frames) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     j2kcuda_sequence* s = j2kcuda_sequence_create(nullptr, -1, 0);
     int rc = j2kcuda_sequence_decode(s, streams, lens, nframes, reduce, frames, nplanes, 0);
     j2kcuda_sequence_destroy(s);
     return rc;
-}
+}); }
 
 }  // extern "C"

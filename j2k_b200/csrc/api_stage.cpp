@@ -36,24 +36,24 @@ int need_device() {
 
 extern "C" {
 
-int j2kcuda_device_count(void) {
+int j2kcuda_device_count(void) { return j2k::guarded([&]() -> int {
     int n = 0;
     if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
     return n;
-}
+}); }
 
-int j2kcuda_init(int device, j2kcuda_log_fn, void*) {
+int j2kcuda_init(int device, j2kcuda_log_fn, void*) { return j2k::guarded([&]() -> int {
     int n = j2kcuda_device_count();
     if (n == 0) return set_error(J2KCUDA_ERR_NO_DEVICE, "no CUDA device: libj2kcuda has no CPU path");
     if (device >= n) return set_error(J2KCUDA_ERR_PARAM, "device ordinal out of range");
     if (device >= 0) CK(cudaSetDevice(device));
     if (const char* err = device_tables_init()) return set_error(J2KCUDA_ERR_CUDA, err);
     return J2KCUDA_OK;
-}
+}); }
 
 void j2kcuda_shutdown(void) { j2k::out_release_all(); }
 
-int j2kcuda_stage_mct(int32_t* c0, int32_t* c1, int32_t* c2, size_t n, int irreversible, int inverse) {
+int j2kcuda_stage_mct(int32_t* c0, int32_t* c1, int32_t* c2, size_t n, int irreversible, int inverse) { return j2k::guarded([&]() -> int {
     if (!c0 || !c1 || !c2) return set_error(J2KCUDA_ERR_PARAM, "null plane");
     if (int rc = need_device()) return rc;
     DevBuf d[3];
@@ -63,9 +63,9 @@ int j2kcuda_stage_mct(int32_t* c0, int32_t* c1, int32_t* c2, size_t n, int irrev
     CK(cudaGetLastError());
     for (int i = 0; i < 3; ++i) CK(cudaMemcpy(h[i], d[i].p, n * 4, cudaMemcpyDeviceToHost));
     return J2KCUDA_OK;
-}
+}); }
 
-int j2kcuda_stage_dwt(int32_t* data, int x0, int y0, int x1, int y1, int numres, int irreversible, int inverse) {
+int j2kcuda_stage_dwt(int32_t* data, int x0, int y0, int x1, int y1, int numres, int irreversible, int inverse) { return j2k::guarded([&]() -> int {
     if (!data || x1 <= x0 || y1 <= y0 || numres < 1 || numres > 33) return set_error(J2KCUDA_ERR_PARAM, "bad region");
     if (int rc = need_device()) return rc;
     const int w = x1 - x0, h = y1 - y0, pitch = (w + 3) & ~3, levels = numres - 1;
@@ -121,11 +121,11 @@ int j2kcuda_stage_dwt(int32_t* data, int x0, int y0, int x1, int y1, int numres,
     }
     CK(cudaGetLastError());
     return J2KCUDA_OK;
-}
+}); }
 
 int j2kcuda_stage_t1_encode(const int32_t* plane, int stride, int height, const int32_t* blk, int nblk, int irreversible,
                             int32_t* numbps, int32_t* npasses, int32_t* rates, int32_t* nmsedec, uint8_t* data,
-                            size_t data_cap, uint64_t* offsets) {
+                            size_t data_cap, uint64_t* offsets) { return j2k::guarded([&]() -> int {
     if (!plane || !blk || nblk < 0 || !numbps || !npasses || !rates || !nmsedec || !data || !offsets)
         return set_error(J2KCUDA_ERR_PARAM, "null argument");
     if (int rc = need_device()) return rc;
@@ -173,6 +173,6 @@ int j2kcuda_stage_t1_encode(const int32_t* plane, int stride, int height, const 
     }
     offsets[nblk] = off;
     return J2KCUDA_OK;
-}
+}); }
 
 }  // extern "C"

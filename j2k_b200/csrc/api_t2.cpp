@@ -10,7 +10,7 @@ using namespace j2k;
 
 extern "C" {
 
-int j2kcuda_version(void) { return J2KCUDA_VERSION; }
+int j2kcuda_version(void) { return j2k::guarded([&]() -> int { return J2KCUDA_VERSION; }); }
 const char* j2kcuda_last_error(void) { return j2k::last_error().c_str(); }
 void j2kcuda_free(void* p) { j2k::out_free(p); }
 
@@ -24,7 +24,7 @@ void j2kcuda_default_params(j2kcuda_params* p) {   // openjpeg.cpp:706-728
     p->device = -1;
 }
 
-int j2kcuda_t2_block_count(const j2kcuda_params* p) {
+int j2kcuda_t2_block_count(const j2kcuda_params* p) { return j2k::guarded([&]() -> int {
     if (!p) return -1;
     if (const char* why = check_params(*p)) { set_error(J2KCUDA_ERR_PARAM, why); return -1; }
     CodingParams cp;
@@ -37,9 +37,9 @@ int j2kcuda_t2_block_count(const j2kcuda_params* p) {
         n += (int)g.cblks.size();
     }
     return n;
-}
+}); }
 
-int j2kcuda_t2_block_geometry(const j2kcuda_params* p, int32_t* geo, int max_blocks) {
+int j2kcuda_t2_block_geometry(const j2kcuda_params* p, int32_t* geo, int max_blocks) { return j2k::guarded([&]() -> int {
     if (!p || !geo) return -1;
     if (const char* why = check_params(*p)) { set_error(J2KCUDA_ERR_PARAM, why); return -1; }
     CodingParams cp;
@@ -62,10 +62,10 @@ int j2kcuda_t2_block_geometry(const j2kcuda_params* p, int32_t* geo, int max_blo
         }
     }
     return n;
-}
+}); }
 
 int j2kcuda_t2_assemble(const j2kcuda_params* p, const j2kcuda_block_result* blocks, int nblocks,
-                        uint8_t** out, size_t* out_len) {
+                        uint8_t** out, size_t* out_len) { return j2k::guarded([&]() -> int {
     if (!p || !blocks || !out || !out_len) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     EncoderHost host;
     setup_coding_params(*p, host.cp);
@@ -92,10 +92,10 @@ int j2kcuda_t2_assemble(const j2kcuda_params* p, const j2kcuda_block_result* blo
     memcpy(*out, cs.data(), cs.size());
     *out_len = cs.size();
     return J2KCUDA_OK;
-}
+}); }
 
 int j2kcuda_join_tile_streams(const j2kcuda_params* p, const uint8_t* const* frags, const size_t* lens, int nfrags,
-                              uint8_t** out, size_t* out_len) {
+                              uint8_t** out, size_t* out_len) { return j2k::guarded([&]() -> int {
     if (!p || !frags || !lens || !out || !out_len || nfrags < 0) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     CodingParams cp;
     setup_coding_params(*p, cp);
@@ -108,6 +108,6 @@ int j2kcuda_join_tile_streams(const j2kcuda_params* p, const uint8_t* const* fra
     memcpy(*out, cs.data(), cs.size());
     *out_len = cs.size();
     return J2KCUDA_OK;
-}
+}); }
 
 }  // extern "C"

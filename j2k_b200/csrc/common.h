@@ -2,6 +2,8 @@
 #pragma once
 #include <cstddef>
 #include <string>
+#include <new>
+#include <exception>
 
 namespace j2k {
 std::string& last_error();                       // thread-local
@@ -10,6 +12,14 @@ int set_error(int code, const std::string& msg); // stores msg, returns code
 void* out_alloc(size_t n);
 void out_free(void* p);
 void out_release_all();                          // j2kcuda_shutdown
+// No C++ exception may cross the C ABI (a std::bad_alloc from a crafted header used to reach std::terminate):
+// every extern "C" entry point runs its body through this.
+template <class F> inline int guarded(F&& f) noexcept {
+    try { return f(); }
+    catch (const std::bad_alloc&) { return set_error(5 /* J2KCUDA_ERR_NOMEM */, "out of host memory"); }
+    catch (const std::exception& e) { return set_error(4 /* J2KCUDA_ERR_STREAM */, std::string("internal error: ") + e.what()); }
+    catch (...) { return set_error(4, "internal error"); }
+}
 }  // namespace j2k
 
 // Internal (not exported through include/j2kcuda.h): shape of the MQ kernel.  A lone frame wants few blocks per warp

@@ -372,7 +372,7 @@ static int download(j2kcuda_decoder* d, const j2kcuda_plane* planes, int nplanes
 
 extern "C" {
 
-j2kcuda_decoder* j2kcuda_decoder_create(int device) {
+j2kcuda_decoder* j2kcuda_decoder_create(int device) { try {
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); set_error(J2KCUDA_ERR_NO_DEVICE, "no CUDA device: libj2kcuda has no CPU path"); return nullptr; }
     j2kcuda_decoder* d = new j2kcuda_decoder();
@@ -384,39 +384,39 @@ j2kcuda_decoder* j2kcuda_decoder_create(int device) {
     ok = ok && cudaEventCreateWithFlags(&d->ev_wait, cudaEventBlockingSync | cudaEventDisableTiming) == cudaSuccess;
     if (!ok) { set_error(J2KCUDA_ERR_CUDA, "decoder_create: CUDA initialisation failed"); free_decoder(d); return nullptr; }
     return d;
-}
+} catch (...) { set_error(J2KCUDA_ERR_NOMEM, "j2kcuda_decoder_create: out of memory or internal error"); return nullptr; } }
 void j2kcuda_decoder_destroy(j2kcuda_decoder* d) { free_decoder(d); }
-int j2kcuda_decoder_prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned reduce) {
+int j2kcuda_decoder_prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned reduce) { return j2k::guarded([&]() -> int {
     if (!d || !bytes) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     d->prepared = false;
     return prepare(d, bytes, n, reduce);
-}
-int j2kcuda_decoder_run(j2kcuda_decoder* d) { return d ? run(d) : set_error(J2KCUDA_ERR_PARAM, "null decoder"); }
-int j2kcuda_decoder_download(j2kcuda_decoder* d, const j2kcuda_plane* planes, int nplanes) {
+}); }
+int j2kcuda_decoder_run(j2kcuda_decoder* d) { return j2k::guarded([&]() -> int { return d ? run(d) : set_error(J2KCUDA_ERR_PARAM, "null decoder"); }); }
+int j2kcuda_decoder_download(j2kcuda_decoder* d, const j2kcuda_plane* planes, int nplanes) { return j2k::guarded([&]() -> int {
     if (!d || !planes) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     return download(d, planes, nplanes);
-}
-int j2kcuda_decoder_get_device_output(j2kcuda_decoder* d, void** d_pixels, int64_t* pitch_bytes, int* sample_type) {
+}); }
+int j2kcuda_decoder_get_device_output(j2kcuda_decoder* d, void** d_pixels, int64_t* pitch_bytes, int* sample_type) { return j2k::guarded([&]() -> int {
     if (!d || !d->ran) return set_error(J2KCUDA_ERR_PARAM, "decoder_run has not completed");
     if (d_pixels) *d_pixels = d->d_out;
     if (pitch_bytes) *pitch_bytes = (int64_t)d->outW * d->ncomp * d->S;
     if (sample_type) *sample_type = d->S == 1 ? J2KCUDA_UCHAR : J2KCUDA_USHORT;
     return J2KCUDA_OK;
-}
-int j2kcuda_decoder_timings(j2kcuda_decoder* d, float* ms, int n) {
+}); }
+int j2kcuda_decoder_timings(j2kcuda_decoder* d, float* ms, int n) { return j2k::guarded([&]() -> int {
     if (!d || !ms) return 0;
     int k = n < 7 ? n : 7;
     for (int i = 0; i < k; ++i) ms[i] = d->ms[i];
     return k;
-}
-int j2kcuda_decoder_counters(j2kcuda_decoder* d, uint64_t* v, int n) {
+}); }
+int j2kcuda_decoder_counters(j2kcuda_decoder* d, uint64_t* v, int n) { return j2k::guarded([&]() -> int {
     if (!d || !v) return 0;
     int k = n < 6 ? n : 6;
     for (int i = 0; i < k; ++i) v[i] = d->counters[i];
     return k;
-}
+}); }
 
-int j2kcuda_probe(const uint8_t* bytes, size_t n, j2kcuda_info* out) {
+int j2kcuda_probe(const uint8_t* bytes, size_t n, j2kcuda_info* out) { return j2k::guarded([&]() -> int {
     if (!bytes || !out) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     size_t off = 0, len = 0; bool jp2 = false;
     if (!find_codestream(bytes, n, off, len, jp2)) return set_error(J2KCUDA_ERR_STREAM, "not a JPEG 2000 codestream or JP2 file");
@@ -427,10 +427,10 @@ int j2kcuda_probe(const uint8_t* bytes, size_t n, j2kcuda_info* out) {
     fill_info(h.cp, out);
     out->is_jp2 = jp2; out->codestream_offset = off; out->codestream_length = len;
     return J2KCUDA_OK;
-}
+}); }
 
 int j2kcuda_decode(const uint8_t* bytes, size_t n, unsigned reduce, const j2kcuda_plane* planes, int nplanes,
-                   j2kcuda_abort_fn abort_fn, void* user) {
+                   j2kcuda_abort_fn abort_fn, void* user) { return j2k::guarded([&]() -> int {
     j2kcuda_decoder* d = j2kcuda_decoder_create(-1);
     if (!d) return J2KCUDA_ERR_NO_DEVICE;
     int rc = j2kcuda_decoder_prepare(d, bytes, n, reduce);
@@ -439,9 +439,9 @@ int j2kcuda_decode(const uint8_t* bytes, size_t n, unsigned reduce, const j2kcud
     if (!rc) rc = j2kcuda_decoder_download(d, planes, nplanes);
     j2kcuda_decoder_destroy(d);
     return rc;
-}
+}); }
 
-int j2kcuda_decoder_copy_to_device(j2kcuda_decoder* d, void* d_pixels, int64_t pitch_bytes) {
+int j2kcuda_decoder_copy_to_device(j2kcuda_decoder* d, void* d_pixels, int64_t pitch_bytes) { return j2k::guarded([&]() -> int {
     if (!d || !d_pixels) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     if (!d->ran) return set_error(J2KCUDA_ERR_PARAM, "decoder_run has not completed");
     const size_t row = (size_t)d->outW * d->ncomp * d->S;
@@ -450,9 +450,9 @@ int j2kcuda_decoder_copy_to_device(j2kcuda_decoder* d, void* d_pixels, int64_t p
     CK(cudaMemcpy2DAsync(d_pixels, (size_t)pitch_bytes, d->d_out, row, row, (size_t)d->outH, cudaMemcpyDeviceToDevice, d->st));
     CK(stream_wait(d->st, d->ev_wait));
     return J2KCUDA_OK;
-}
+}); }
 
-int j2kcuda_t2_parse(const uint8_t* bytes, size_t n, unsigned reduce, int32_t** blkinfo, int* nblocks, uint8_t** seg, size_t* seg_len) {
+int j2kcuda_t2_parse(const uint8_t* bytes, size_t n, unsigned reduce, int32_t** blkinfo, int* nblocks, uint8_t** seg, size_t* seg_len) { return j2k::guarded([&]() -> int {
     if (!bytes || !blkinfo || !nblocks || !seg || !seg_len) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     size_t off = 0, len = 0; bool jp2 = false;
     if (!find_codestream(bytes, n, off, len, jp2)) return set_error(J2KCUDA_ERR_STREAM, "not a JPEG 2000 codestream or JP2 file");
@@ -474,9 +474,9 @@ int j2kcuda_t2_parse(const uint8_t* bytes, size_t n, unsigned reduce, int32_t** 
         }
     *blkinfo = info; *nblocks = nb; *seg = data; *seg_len = total;
     return J2KCUDA_OK;
-}
+}); }
 
-int j2kcuda_stage_t1_decode(const uint8_t* data, const int32_t* blk, int nblk, int32_t* out) {
+int j2kcuda_stage_t1_decode(const uint8_t* data, const int32_t* blk, int nblk, int32_t* out) { return j2k::guarded([&]() -> int {
     if (!data || !blk || !out || nblk < 0) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return set_error(J2KCUDA_ERR_NO_DEVICE, "no CUDA device: libj2kcuda has no CPU path"); }
@@ -511,6 +511,6 @@ int j2kcuda_stage_t1_decode(const uint8_t* data, const int32_t* blk, int nblk, i
     cudaFree(d_out); cudaFree(d_seg); cudaFree(d_blk);
     if (e != cudaSuccess) return set_error(J2KCUDA_ERR_CUDA, cudaGetErrorString(e));
     return J2KCUDA_OK;
-}
+}); }
 
 }  // extern "C"

@@ -328,18 +328,18 @@ static int upload_planes(j2kcuda_encoder* e, const j2kcuda_plane* planes, int np
 
 extern "C" {
 
-j2kcuda_encoder* j2kcuda_encoder_create(const j2kcuda_params* p) {
+j2kcuda_encoder* j2kcuda_encoder_create(const j2kcuda_params* p) { try {
     if (!p) { set_error(J2KCUDA_ERR_PARAM, "null params"); return nullptr; }
     j2kcuda_encoder* e = new j2kcuda_encoder();
     for (auto& ev : e->ev) ev = nullptr;
     e->p = *p;
     if (setup_encoder(e) != J2KCUDA_OK) { free_encoder(e); return nullptr; }
     return e;
-}
+} catch (...) { set_error(J2KCUDA_ERR_NOMEM, "j2kcuda_encoder_create: out of memory or internal error"); return nullptr; } }
 
 void j2kcuda_encoder_destroy(j2kcuda_encoder* e) { free_encoder(e); }
 
-int j2kcuda_encoder_upload(j2kcuda_encoder* e, const j2kcuda_plane* planes, int nplanes) {
+int j2kcuda_encoder_upload(j2kcuda_encoder* e, const j2kcuda_plane* planes, int nplanes) { return j2k::guarded([&]() -> int {
     if (!e || !planes) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     CK(cudaSetDevice(e->device));
     CK(cudaEventRecord(e->ev[8], e->st));
@@ -347,9 +347,9 @@ int j2kcuda_encoder_upload(j2kcuda_encoder* e, const j2kcuda_plane* planes, int 
     if (rc) return rc;
     CK(cudaEventRecord(e->ev[9], e->st));
     return J2KCUDA_OK;
-}
+}); }
 
-int j2kcuda_encoder_set_device_input(j2kcuda_encoder* e, const void* d_pixels, int64_t pitch_bytes, int sample_type) {
+int j2kcuda_encoder_set_device_input(j2kcuda_encoder* e, const void* d_pixels, int64_t pitch_bytes, int sample_type) { return j2k::guarded([&]() -> int {
     if (!e || !d_pixels) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     const int S = sample_bytes_of(sample_type);
     memset(&e->src, 0, sizeof(e->src));
@@ -368,9 +368,9 @@ int j2kcuda_encoder_set_device_input(j2kcuda_encoder* e, const void* d_pixels, i
     e->counters[4] = 0;
     e->have_input = true;
     return J2KCUDA_OK;
-}
+}); }
 
-int j2kcuda_encoder_run(j2kcuda_encoder* e) {
+int j2kcuda_encoder_run(j2kcuda_encoder* e) { return j2k::guarded([&]() -> int {
     if (!e) return set_error(J2KCUDA_ERR_PARAM, "null encoder");
     if (!e->have_input) return set_error(J2KCUDA_ERR_PARAM, "no input uploaded");
     CK(cudaSetDevice(e->device));
@@ -439,9 +439,9 @@ int j2kcuda_encoder_run(j2kcuda_encoder* e) {
     e->counters[5] = (uint64_t)e->nblocks * sizeof(T1Result) + ((uint64_t)e->nblocks + 1) * 4 + packed;
     e->ran = true;
     return J2KCUDA_OK;
-}
+}); }
 
-int j2kcuda_encoder_finish(j2kcuda_encoder* e, uint8_t** out, size_t* out_len) {
+int j2kcuda_encoder_finish(j2kcuda_encoder* e, uint8_t** out, size_t* out_len) { return j2k::guarded([&]() -> int {
     if (!e || !out || !out_len) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     if (!e->ran) return set_error(J2KCUDA_ERR_PARAM, "encoder_run has not completed");
     auto t0 = std::chrono::steady_clock::now();
@@ -486,23 +486,23 @@ int j2kcuda_encoder_finish(j2kcuda_encoder* e, uint8_t** out, size_t* out_len) {
     *out_len = cs.size();
     e->ms[6] = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
     return J2KCUDA_OK;
-}
+}); }
 
-int j2kcuda_encoder_timings(j2kcuda_encoder* e, float* ms, int n) {
+int j2kcuda_encoder_timings(j2kcuda_encoder* e, float* ms, int n) { return j2k::guarded([&]() -> int {
     if (!e || !ms) return 0;
     int k = n < 8 ? n : 8;
     for (int i = 0; i < k; ++i) ms[i] = e->ms[i];
     return k;
-}
+}); }
 
-int j2kcuda_encoder_counters(j2kcuda_encoder* e, uint64_t* v, int n) {
+int j2kcuda_encoder_counters(j2kcuda_encoder* e, uint64_t* v, int n) { return j2k::guarded([&]() -> int {
     if (!e || !v) return 0;
     int k = n < 6 ? n : 6;
     for (int i = 0; i < k; ++i) v[i] = e->counters[i];
     return k;
-}
+}); }
 
-int j2kcuda_encode(const j2kcuda_params* p, const j2kcuda_plane* planes, int nplanes, uint8_t** out, size_t* out_len) {
+int j2kcuda_encode(const j2kcuda_params* p, const j2kcuda_plane* planes, int nplanes, uint8_t** out, size_t* out_len) { return j2k::guarded([&]() -> int {
     j2kcuda_encoder* e = j2kcuda_encoder_create(p);
     if (!e) return J2KCUDA_ERR_PARAM;
     int rc = j2kcuda_encoder_upload(e, planes, nplanes);
@@ -510,7 +510,7 @@ int j2kcuda_encode(const j2kcuda_params* p, const j2kcuda_plane* planes, int npl
     if (!rc) rc = j2kcuda_encoder_finish(e, out, out_len);
     j2kcuda_encoder_destroy(e);
     return rc;
-}
+}); }
 
 }  // extern "C"
 

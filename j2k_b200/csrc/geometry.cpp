@@ -47,6 +47,32 @@ void calc_explicit_stepsizes(CompParams& c) { // dwt.cpp:401-408,573-593
     }
 }
 
+// Upper bounds of what build_tile would allocate, in 64-bit arithmetic and without allocating: a 60-byte header that
+// announces 2^30 x 2^30 samples or one-sample precincts must give an error, not std::bad_alloc.
+bool geometry_within_limits(const CodingParams& cp, std::string& err) {
+    const uint64_t ntiles = (uint64_t)cp.tw * cp.th;
+    const uint64_t tw = std::min<uint64_t>(cp.tdx, (uint64_t)cp.x1 - cp.tx0), th = std::min<uint64_t>(cp.tdy, (uint64_t)cp.y1 - cp.ty0);
+    uint64_t precs = 0, blocks = 0;
+    for (int c = 0; c < cp.ncomp; ++c) {
+        const CompParams& tc = cp.comps[c];
+        const uint64_t cw = tw / (uint64_t)tc.dx + 1, ch = th / (uint64_t)tc.dy + 1;
+        for (int r = 0; r < tc.numres; ++r) {
+            const int level = tc.numres - 1 - r;
+            const uint64_t rw = (cw >> level) + 1, rh = (ch >> level) + 1;
+            int pdx = tc.prcw[r], pdy = tc.prch[r];
+            if (r > 0 && (pdx < 1 || pdy < 1)) { err = "invalid precinct size"; return false; }
+            const uint64_t pw = (rw >> pdx) + 2, ph = (rh >> pdy) + 2;
+            const int cbw = std::min(tc.cblkw, r ? pdx - 1 : pdx), cbh = std::min(tc.cblkh, r ? pdy - 1 : pdy);
+            const uint64_t nb = r ? 3 : 1;
+            precs += pw * ph * nb;
+            blocks += ((rw >> cbw) + pw + 1) * ((rh >> cbh) + ph + 1) * nb;
+        }
+    }
+    if (blocks * ntiles > (1ull << 23) || blocks > (1ull << 22)) { err = "more than 2^23 code-blocks"; return false; }
+    if (precs * ntiles * (uint64_t)std::max(cp.numlayers, 1) > (1ull << 27) || precs > (1ull << 22)) { err = "more than 2^27 packets"; return false; }
+    return true;
+}
+
 void build_tile(const CodingParams& cp, int tileno, float fraction, TileGeo& t) {
     t.tileno = tileno;
     t.comps.clear();
@@ -83,7 +109,7 @@ void build_tile(const CodingParams& cp, int tileno, float fraction, TileGeo& t) 
             uint32_t bry = ceildivpow2((uint32_t)rg.r.y1, pdy) << pdy;
             rg.pw = rg.r.x0 == rg.r.x1 ? 0 : (int)((brx - tlx) >> pdx);
             rg.ph = rg.r.y0 == rg.r.y1 ? 0 : (int)((bry - tly) >> pdy);
-            int nprec = rg.pw * rg.ph;
+            int nprec = (int)std::min<int64_t>((int64_t)rg.pw * rg.ph, 1 << 22);     // geometry_within_limits() ran first
             uint32_t tlcbgx, tlcbgy;
             int cbgw, cbgh;
             if (resno == 0) { tlcbgx = tlx; tlcbgy = tly; cbgw = pdx; cbgh = pdy; rg.numbands = 1; }

@@ -108,6 +108,7 @@ inline int floorlog2(uint32_t a) { int l = 0; while (a > 1) { a >>= 1; ++l; } re
 
 // fraction = 1.0 for the encoder, 0.5 for the decoder (tcd.cpp:876,888)
 void build_tile(const CodingParams& cp, int tileno, float fraction, TileGeo& out);
+bool geometry_within_limits(const CodingParams& cp, std::string& err);   // call before build_tile on untrusted parameters
 
 // dwt.cpp:193-208, 531-593; mct.cpp:73,78
 double dwt_norm(int level, int orient, bool real);

@@ -57,7 +57,7 @@ double res_value(uint32_t num, uint32_t den, int exponent) {    // jp2.cpp:696-7
 
 extern "C" {
 
-int j2kcuda_probe_jp2(const uint8_t* d, size_t n, j2kcuda_jp2_info* out) {
+int j2kcuda_probe_jp2(const uint8_t* d, size_t n, j2kcuda_jp2_info* out) { return j2k::guarded([&]() -> int {
     if (!d || !out) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     memset(out, 0, sizeof(*out));
     if (n >= 2 && d[0] == 0xff && d[1] == 0x4f) {                 // raw codestream (SOC)
@@ -169,9 +169,9 @@ int j2kcuda_probe_jp2(const uint8_t* d, size_t n, j2kcuda_jp2_info* out) {
         pos = next;
     }
     return set_error(J2KCUDA_ERR_STREAM, "JP2 file without a codestream box");
-}
+}); }
 
-int j2kcuda_jp2_palette(const uint8_t* d, size_t n, uint32_t* entries, size_t cap) {
+int j2kcuda_jp2_palette(const uint8_t* d, size_t n, uint32_t* entries, size_t cap) { return j2k::guarded([&]() -> int {
     j2kcuda_jp2_info info;
     const int rc = j2kcuda_probe_jp2(d, n, &info);
     if (rc) return -rc;
@@ -186,9 +186,9 @@ int j2kcuda_jp2_palette(const uint8_t* d, size_t n, uint32_t* entries, size_t ca
             q += nb;
         }
     return (int)total;
-}
+}); }
 
-int j2kcuda_wrap_jp2(const uint8_t* cs, size_t len, const j2kcuda_jp2_params* p, uint8_t** out, size_t* out_len) {
+int j2kcuda_wrap_jp2(const uint8_t* cs, size_t len, const j2kcuda_jp2_params* p, uint8_t** out, size_t* out_len) { return j2k::guarded([&]() -> int {
     if (!cs || !p || !out || !out_len) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     if (p->ncomp == 0 || p->ncomp > J2KCUDA_JP2_MAX_CHANNELS) return set_error(J2KCUDA_ERR_PARAM, "1..16 components");
     if (len > 0xffffffffull - 8) return set_error(J2KCUDA_ERR_UNSUPPORTED, "codestream too long for a 32-bit box length");
@@ -240,6 +240,6 @@ int j2kcuda_wrap_jp2(const uint8_t* cs, size_t len, const j2kcuda_jp2_params* p,
     memcpy(buf + v.size(), cs, len);
     *out = buf; *out_len = v.size() + len;
     return J2KCUDA_OK;
-}
+}); }
 
 }  // extern "C"

@@ -10,22 +10,35 @@ namespace {
 
 struct Rd {
     const uint8_t* d; size_t n; size_t pos;
-    bool ok(size_t k) const { return pos + k <= n; }
-    uint32_t u(int bytes) { uint32_t v = 0; for (int i = 0; i < bytes; ++i) v = (v << 8) | d[pos++]; return v; }
+    bool bad = false;                                  // a read past the end: returns 0, the caller reports the marker as damaged
+    bool ok(size_t k) const { return k <= n && pos <= n - k; }
+    uint32_t u(int bytes) {
+        if (!ok((size_t)bytes)) { bad = true; pos = n; return 0; }
+        uint32_t v = 0; for (int i = 0; i < bytes; ++i) v = (v << 8) | d[pos++]; return v;
+    }
 };
 
-void read_spcod(Rd& r, size_t end, CompParams& t, bool has_prec) {     // j2k.cpp:8372-8470
+bool read_spcod(Rd& r, size_t end, CompParams& t, bool has_prec) {     // j2k.cpp:8372-8470
+    if (r.pos + 5 > end) return false;
     t.numres = (int)r.u(1) + 1;
     t.cblkw = (int)r.u(1) + 2; t.cblkh = (int)r.u(1) + 2;
     t.cblksty = (int)r.u(1); t.qmfbid = (int)r.u(1);
     for (int i = 0; i < MAX_RES; ++i) t.prcw[i] = t.prch[i] = 15;
     if (has_prec)
-        for (int i = 0; i < t.numres && i < MAX_RES && r.pos < end; ++i) { uint32_t v = r.u(1); t.prcw[i] = v & 15; t.prch[i] = v >> 4; }
+        for (int i = 0; i < t.numres && i < MAX_RES; ++i) {
+            if (r.pos >= end) return false;
+            uint32_t v = r.u(1); t.prcw[i] = v & 15; t.prch[i] = v >> 4;
+            if (i > 0 && (t.prcw[i] == 0 || t.prch[i] == 0)) return false;     // "Invalid precinct size", j2k.cpp:8445
+        }
+    return true;
 }
-void read_sqcd(Rd& r, size_t end, CompParams& t) {                     // j2k.cpp:8662-8760
+bool read_sqcd(Rd& r, size_t end, CompParams& t) {                     // j2k.cpp:8662-8760
+    if (r.pos + 1 > end) return false;
     uint32_t v = r.u(1);
     t.qntsty = v & 31; t.numgbits = v >> 5;
+    if (t.qntsty > 2) return false;
     int nb = t.qntsty == 1 ? 1 : (t.qntsty == 0 ? (int)(end - r.pos) : (int)(end - r.pos) / 2);
+    if (nb < 1 || (t.qntsty == 1 && r.pos + 2 > end)) return false;
     for (int b = 0; b < nb && b < 3 * MAX_RES; ++b) {
         if (t.qntsty == 0) { t.steps[b].expn = (int)(r.u(1) >> 3); t.steps[b].mant = 0; }
         else { uint32_t s = r.u(2); t.steps[b].expn = (int)(s >> 11); t.steps[b].mant = (int)(s & 0x7ff); }
@@ -36,6 +49,7 @@ void read_sqcd(Rd& r, size_t end, CompParams& t) {                     // j2k.cp
             t.steps[b].expn = e > 0 ? e : 0; t.steps[b].mant = t.steps[0].mant;
         }
     r.pos = end;
+    return true;
 }
 
 int getnumpasses(BitReader& bio) {                                      // t2.cpp:225-239
@@ -104,6 +118,9 @@ bool DecoderHost::parse_main_header(const uint8_t* d, size_t n, size_t& pos, std
                 if (!cp.comps[c].dx || !cp.comps[c].dy || cp.comps[c].prec > 31) { err = "bad SIZ component"; return false; }
                 cp.comps[c].dc_shift = cp.comps[c].sgnd ? 0 : 1 << (cp.comps[c].prec - 1);
             }
+            // the first tile must meet the image (j2k.cpp:2098-2106), and the sizes must stay allocatable
+            if ((uint64_t)cp.tx0 + cp.tdx <= cp.x0 || (uint64_t)cp.ty0 + cp.tdy <= cp.y0) { err = "bad SIZ: the first tile lies outside the image"; return false; }
+            if (cp.x1 - cp.x0 > (1u << 24) || cp.y1 - cp.y0 > (1u << 24) || (uint64_t)(cp.x1 - cp.x0) * (cp.y1 - cp.y0) > (1ull << 30)) { err = "image larger than 2^30 samples per component"; return false; }
             cp.tw = ceildiv(cp.x1 - cp.tx0, cp.tdx); cp.th = ceildiv(cp.y1 - cp.ty0, cp.tdy);
             if ((uint64_t)cp.tw * cp.th > 65535) { err = "too many tiles"; return false; }
             have_siz = true;
@@ -111,9 +128,11 @@ bool DecoderHost::parse_main_header(const uint8_t* d, size_t n, size_t& pos, std
         }
         case 0xff52: {                                                   // COD, j2k.cpp:2422-2507
             if (!have_siz) { err = "COD before SIZ"; return false; }
+            if (L < 12) { err = "bad COD"; return false; }
             cp.csty = (int)r.u(1); cp.prog = (int)r.u(1); cp.numlayers = (int)r.u(2); cp.mct = (int)r.u(1);
             CompParams t = cp.comps[0];
-            read_spcod(r, end, t, cp.csty & 1);
+            if (!read_spcod(r, end, t, cp.csty & 1)) { err = "bad COD"; return false; }
+            if (cp.numlayers < 1) { err = "bad COD: no layers"; return false; }
             for (int c = 0; c < cp.ncomp; ++c) {
                 if (coc_seen[c]) continue;
                 CompParams& o = cp.comps[c];
@@ -126,17 +145,18 @@ bool DecoderHost::parse_main_header(const uint8_t* d, size_t n, size_t& pos, std
         }
         case 0xff53: {                                                   // COC, j2k.cpp:2618-2698
             if (!have_siz) { err = "COC before SIZ"; return false; }
+            if (L < 9) { err = "bad COC"; return false; }
             uint32_t c = r.u(cp.ncomp <= 256 ? 1 : 2);
             if ((int)c >= cp.ncomp) { err = "bad COC"; return false; }
             cp.comps[c].csty = (int)r.u(1) & 1;
-            read_spcod(r, end, cp.comps[c], cp.comps[c].csty & 1);
+            if (!read_spcod(r, end, cp.comps[c], cp.comps[c].csty & 1)) { err = "bad COC"; return false; }
             coc_seen[c] = true;
             break;
         }
         case 0xff5c: {                                                   // QCD
             if (!have_siz) { err = "QCD before SIZ"; return false; }
             CompParams t;
-            read_sqcd(r, end, t);
+            if (L < 4 || !read_sqcd(r, end, t)) { err = "bad QCD"; return false; }
             for (int c = 0; c < cp.ncomp; ++c) {
                 if (qcc_seen[c]) continue;
                 cp.comps[c].qntsty = t.qntsty; cp.comps[c].numgbits = t.numgbits;
@@ -149,7 +169,7 @@ bool DecoderHost::parse_main_header(const uint8_t* d, size_t n, size_t& pos, std
             if (!have_siz) { err = "QCC before SIZ"; return false; }
             uint32_t c = r.u(cp.ncomp <= 256 ? 1 : 2);
             if ((int)c >= cp.ncomp) { err = "bad QCC"; return false; }
-            read_sqcd(r, end, cp.comps[c]);
+            if (!read_sqcd(r, end, cp.comps[c])) { err = "bad QCC"; return false; }
             qcc_seen[c] = true;
             break;
         }
@@ -167,6 +187,7 @@ bool DecoderHost::parse_main_header(const uint8_t* d, size_t n, size_t& pos, std
         default: break;                                                  // TLM, PLM, PPM(!), CRG, COM ...
         }
         if (m == 0xff60) { err = "packed packet headers (PPM) are not supported"; return false; }
+        if (r.bad) { err = "marker segment shorter than its contents"; return false; }
         r.pos = end;
     }
     if (!have_siz || !have_cod || !have_qcd) { err = "main header lacks SIZ, COD or QCD"; return false; }
@@ -212,7 +233,7 @@ static bool read_packet(const CodingParams& cp, DecTile& t, const PacketId& pk, 
     }
     BitReader bio;
     bio.init(d + pos, end - pos);
-    struct Inc { int blk; int len; };
+    struct Inc { int blk; uint32_t len; };
     Inc inc[4096];
     int ninc = 0;
     std::vector<Inc> big;
@@ -242,8 +263,9 @@ static bool read_packet(const CodingParams& cp, DecTile& t, const PacketId& pk, 
                 while (bio.getbit()) { if (++incr > 32) { err = "bad Lblock"; return false; } }
                 cb.numlenbits += incr;
                 const int nbits = cb.numlenbits + floorlog2((uint32_t)np);
-                if (nbits > 32) { err = "bad segment length field"; return false; }
-                const int len = (int)bio.read(nbits);
+                if (nbits > 31) { err = "bad segment length field"; return false; }     // a 32-bit length used to wrap to -1
+                const uint32_t len = bio.read(nbits);
+                if (len > end - pos) { err = "code-block segment longer than the tile-part"; return false; }
                 cb.npasses += np;
                 if (ninc < 4096) inc[ninc++] = Inc{prc.first_cblk + k, len};
                 else big.push_back(Inc{prc.first_cblk + k, len});
@@ -257,10 +279,11 @@ static bool read_packet(const CodingParams& cp, DecTile& t, const PacketId& pk, 
         if (pos + 2 <= end && d[pos] == 0xff && d[pos + 1] == 0x92) pos += 2;
     }
     auto body = [&](const Inc& in) {
-        if (pos + (size_t)in.len > end) return false;
+        if (pos > end || (size_t)in.len > end - pos) return false;
         DecBlock& cb = t.blocks[in.blk];
-        if (in.len) cb.chunks.emplace_back((uint32_t)pos, (uint32_t)in.len);
-        cb.len += in.len;
+        if ((uint64_t)cb.len + in.len > (1u << 30)) return false;
+        if (in.len) cb.chunks.emplace_back((uint32_t)pos, in.len);
+        cb.len += (int)in.len;
         pos += (size_t)in.len;
         return true;
     };
@@ -272,6 +295,7 @@ static bool read_packet(const CodingParams& cp, DecTile& t, const PacketId& pk, 
 bool DecoderHost::parse(const uint8_t* d, size_t n, std::string& err) {
     size_t pos = 0;
     if (!parse_main_header(d, n, pos, err)) return false;
+    if (!geometry_within_limits(cp, err)) return false;
     const int nt = (int)(cp.tw * cp.th);
     tiles.assign(nt, DecTile());
     std::vector<std::vector<PocEntry>> tile_pocs(nt);

@@ -180,3 +180,63 @@ def test_truncated_and_corrupt_streams_are_rejected_by_the_parser():
         for k in rng.integers(2, 120, size=3):
             bad[int(k)] = int(rng.integers(0, 256))
         assert parse(bytes(bad)) in (0, L.ERR_STREAM, L.ERR_UNSUPPORTED, L.ERR_PARAM)
+
+
+# ---- crafted headers and packets: a status and a message, never a fault, an abort or an over-read ----
+def _hdr(w=64, h=64, tdx=None, tdy=None, x0=0, y0=0, tx0=0, ty0=0, ncomp=1, layers=1, numres=1, csty=0, prec_bytes=b"", qcd=None):
+    import struct
+    tdx = w if tdx is None else tdx
+    tdy = h if tdy is None else tdy
+    siz = struct.pack(">HIIIIIIIIH", 0, w, h, x0, y0, tdx, tdy, tx0, ty0, ncomp) + b"\x07\x01\x01" * ncomp
+    cod = struct.pack(">BBHB", csty, 0, layers, 0) + bytes([numres - 1, 4, 4, 0, 1]) + prec_bytes
+    qcd = bytes([0x40]) + bytes([8 << 3] * (3 * numres - 2)) if qcd is None else qcd
+    seg = lambda m, b: struct.pack(">HH", m, len(b) + 2) + b
+    return b"\xff\x4f" + seg(0xff51, siz) + seg(0xff52, cod) + seg(0xff5c, qcd)
+
+
+def _parse(data):
+    lib = L.lib()
+    info = C.POINTER(C.c_int32)(); nb = C.c_int(0); seg = C.POINTER(C.c_uint8)(); n = C.c_size_t(0)
+    rc = lib.j2kcuda_t2_parse(data, C.c_size_t(len(data)), 0, C.byref(info), C.byref(nb), C.byref(seg), C.byref(n))
+    if rc == 0:
+        lib.j2kcuda_free(info); lib.j2kcuda_free(seg)
+    return rc
+
+
+def _tile(body):
+    import struct
+    return b"\xff\x90" + struct.pack(">HHIBB", 10, 0, 14 + len(body), 0, 1) + b"\xff\x93" + body + b"\xff\xd9"
+
+
+def test_segment_length_of_32_one_bits_is_rejected():
+    # packet header: non-empty, block included, 0 missing bit-planes, 1 pass, Lblock grown by 29 (3 + 29 = 32 bits),
+    # then a length of 32 one-bits: read as int this was -1 and passed the bounds check (heap overflow, ADVICE high)
+    bits = "1" + "1" + "1" + "0" + "1" * 29 + "0" + "1" * 32
+    by = bytearray()
+    acc, cnt, lim = 0, 0, 8
+    for b in bits + "0" * 16:                          # bit-stuffed like bio.cpp: 7 bits after a 0xff byte
+        acc = (acc << 1) | int(b); cnt += 1
+        if cnt == lim:
+            by.append(acc); lim = 7 if acc == 0xff else 8; acc = 0; cnt = 0
+    data = _hdr() + _tile(bytes(by) + b"\x00" * 64)
+    assert _parse(data) == L.ERR_STREAM and L.last_error()
+
+
+def test_giant_and_degenerate_geometry_is_refused_before_any_allocation():
+    for hdr in (_hdr(w=1 << 30, h=1 << 30),                                  # 2^60 samples
+                _hdr(w=1 << 20, h=1 << 10, numres=1, csty=1, prec_bytes=b"\x00"),   # one-sample precincts over a megapixel
+                _hdr(w=1024, h=1024, layers=65535, numres=6, csty=1, prec_bytes=b"\x22" * 6),   # 65535 layers x 87 000 precincts
+                _hdr(w=64, h=64, x0=40, y0=40, tdx=16, tdy=16),               # first tile ends before the image starts
+                _hdr(w=64, h=64, numres=3, csty=1, prec_bytes=b"\x88\x80\x88")):   # precinct exponent 0 above resolution 0 (j2k.cpp:8445)
+        assert _parse(hdr + _tile(b"\x00" * 16)) in (L.ERR_STREAM, L.ERR_NOMEM, L.ERR_UNSUPPORTED), L.last_error()
+        assert L.last_error()
+
+
+def test_marker_segments_shorter_than_their_contents():
+    import struct
+    good = _hdr()
+    assert _parse(good + _tile(b"\x80" + b"\x00" * 8)) in (0, L.ERR_STREAM)
+    siz_end = 2 + 4 + 38 + 3
+    for marker, L_ in ((0xff52, 3), (0xff52, 11), (0xff53, 4), (0xff5c, 3), (0xff5d, 3)):
+        bad = good[:siz_end] + struct.pack(">HH", marker, L_) + b"\x00" * (L_ - 2)     # segment ends the buffer: the old reader ran past it
+        assert _parse(bad) == L.ERR_STREAM and L.last_error()
