@@ -7,9 +7,47 @@
 
 #include <vector>
 #include <string>
+#include <cstdlib>
+#include <cstring>
+#include <cstdio>
 
 namespace j2k
 {
+
+// How much of CompressionSettings WriteFile honours.
+//   AS_WRITTEN  exactly what OpenJPEGCodec::WriteFile passes on today (src/common/j2k_openjpeg_codec.cpp:703-719): the number
+//               of layers, cp_disto_alloc and the tile size; everything else is the library default (lossless 5/3, no MCT,
+//               6 resolutions, 64x64 code-blocks, LRCP, raw codestream).  Output is byte-identical to the reference codec's
+//               (tests/test_integration_plugin.py).
+//   FULL        (default) also what the reference marks "TODO: copy more settings": reversible / irreversible, size and
+//               quality targets, progression order, the DCI profiles, RCT/ICT for RGB, JP2 / JPX wrapping.
+// Chosen by CudaCodec::SetMode() or the environment variable J2K_CUDA_CODEC_MODE=as-written|full.
+static int g_mode = -1;
+void CudaCodec::SetMode(Mode m) { g_mode = m; }
+CudaCodec::Mode CudaCodec::GetMode()
+{
+	if(g_mode < 0)
+	{
+		const char *e = getenv("J2K_CUDA_CODEC_MODE");
+		g_mode = (e != NULL && strcmp(e, "as-written") == 0) ? AS_WRITTEN : FULL;
+	}
+	return static_cast<Mode>(g_mode);
+}
+
+static void LogToStdout(void *, int level, const char *msg)       // the reference prints library messages (j2k_openjpeg_codec.cpp:156-172)
+{
+	printf("libj2kcuda %s: %s\n", (level == 0 ? "error" : "info"), msg);
+}
+
+static void InitOnce()
+{
+	static bool done = false;
+	if(!done)
+	{
+		j2kcuda_init(-1, LogToStdout, NULL);
+		done = true;
+	}
+}
 
 static std::vector<uint8_t> ReadAll(InputFile &file)
 {
@@ -47,6 +85,7 @@ static void ToPlanes(const Buffer &buffer, j2kcuda_plane planes[J2K_CODEC_MAX_CH
 
 void CudaCodec::GetFileInfo(InputFile &file, FileInfo &info)
 {
+	InitOnce();
 	const std::vector<uint8_t> bytes = ReadAll(file);
 	j2kcuda_info hdr;
 	Check( j2kcuda_probe(bytes.empty() ? NULL : &bytes[0], bytes.size(), &hdr) );
@@ -125,6 +164,7 @@ void CudaCodec::GetFileInfo(InputFile &file, FileInfo &info)
 
 void CudaCodec::ReadFile(InputFile &file, const Buffer &buffer, unsigned int subsample, Progress *progress)
 {
+	InitOnce();
 	const std::vector<uint8_t> bytes = ReadAll(file);
 	unsigned int reduce = 0;                     // cp_reduce = log2(subsample), j2k_openjpeg_codec.cpp:496-501
 	while((1u << (reduce + 1)) <= subsample)
@@ -141,6 +181,9 @@ void CudaCodec::ReadFile(InputFile &file, const Buffer &buffer, unsigned int sub
 
 void CudaCodec::WriteFile(OutputFile &file, const FileInfo &info, const Buffer &buffer, Progress *progress)
 {
+	InitOnce();
+	const bool asWritten = (GetMode() == AS_WRITTEN);
+
 	j2kcuda_params p;
 	j2kcuda_default_params(&p);
 	p.width = info.width;
@@ -148,34 +191,49 @@ void CudaCodec::WriteFile(OutputFile &file, const FileInfo &info, const Buffer &
 	p.ncomp = buffer.channels;
 	p.prec = info.depth;
 	p.sgnd = 0;
-	p.mct = (buffer.channels >= 3 ? 1 : 0);      // what opj_compress does for RGB (bin/jp2/opj_compress.cpp:1399-1400)
 
 	const CompressionSettings &s = info.settings;
-	p.numlayers = (s.method == LOSSLESS ? 1 : s.layers);
+	const unsigned int maxLayers = sizeof(p.rates) / sizeof(p.rates[0]);
+	const unsigned int layers = (s.layers < 1 ? 1 : s.layers > maxLayers ? maxLayers : s.layers);
 	if(s.tileSize && (s.tileSize < info.width || s.tileSize < info.height))
 		p.tile_w = p.tile_h = s.tileSize;
-	p.prog_order = (s.order == LRCP ? J2KCUDA_LRCP : s.order == RLCP ? J2KCUDA_RLCP : s.order == RPCL ? J2KCUDA_RPCL :
-					s.order == PCRL ? J2KCUDA_PCRL : J2KCUDA_CPRL);
 
-	if(s.method == CINEMA)
+	if(asWritten)
 	{
-		p.profile = (s.dciProfile == DCI_4K ? J2KCUDA_PROFILE_CINEMA_4K : J2KCUDA_PROFILE_CINEMA_2K);
-		p.max_cs_size = s.fileSize * 1024;        // the caller pre-computes KiB per frame (src/aftereffects/j2k.cpp:817-830)
+		p.mct = 0;                               // library default tcp_mct (openjpeg.cpp:706-728); the reference never sets it
+		p.numlayers = layers;                    // params.tcp_numlayers = info.settings.layers, all rates 0: lossless layers
 	}
-	else if(s.method == SIZE)
+	else
 	{
-		p.irreversible = !s.reversible;
-		const double raw = (double)info.width * info.height * buffer.channels * info.depth / 8.0;
-		p.rates[p.numlayers - 1] = raw / ((double)s.fileSize * 1024.0);
-		for(int i = (int)p.numlayers - 2; i >= 0; i--)
-			p.rates[i] = p.rates[i + 1] * 2.0;
-	}
-	else if(s.method == QUALITY)
-	{
-		p.irreversible = !s.reversible;
-		p.rates[p.numlayers - 1] = 1.0 + (100 - s.quality) * 0.5;   // quality slider -> compression ratio
-		for(int i = (int)p.numlayers - 2; i >= 0; i--)
-			p.rates[i] = p.rates[i + 1] * 2.0;
+		p.mct = (buffer.channels >= 3 ? 1 : 0);  // what opj_compress does for RGB (bin/jp2/opj_compress.cpp:1399-1400)
+		p.numlayers = (s.method == LOSSLESS ? 1 : layers);
+		p.prog_order = (s.order == LRCP ? J2KCUDA_LRCP : s.order == RLCP ? J2KCUDA_RLCP : s.order == RPCL ? J2KCUDA_RPCL :
+						s.order == PCRL ? J2KCUDA_PCRL : J2KCUDA_CPRL);
+
+		if(s.method == CINEMA)
+		{
+			p.profile = (s.dciProfile == DCI_4K ? J2KCUDA_PROFILE_CINEMA_4K : J2KCUDA_PROFILE_CINEMA_2K);
+			p.max_cs_size = s.fileSize * 1024;   // the caller pre-computes KiB per frame (src/aftereffects/j2k.cpp:817-830); 0 = profile default
+		}
+		else if(s.method == SIZE)
+		{
+			if(s.fileSize == 0)
+				throw Exception("Target file size is zero.");
+			p.irreversible = !s.reversible;
+			const double raw = (double)info.width * info.height * buffer.channels * info.depth / 8.0;
+			const double ratio = raw / ((double)s.fileSize * 1024.0);
+			p.rates[p.numlayers - 1] = (ratio > 1.0 ? ratio : 1.0);
+			for(int i = (int)p.numlayers - 2; i >= 0; i--)
+				p.rates[i] = p.rates[i + 1] * 2.0;
+		}
+		else if(s.method == QUALITY)
+		{
+			p.irreversible = !s.reversible;
+			const int q = (s.quality > 100 ? 100 : s.quality);
+			p.rates[p.numlayers - 1] = 1.0 + (100 - q) * 0.5;   // quality slider -> compression ratio (the reference has no mapping: "TODO")
+			for(int i = (int)p.numlayers - 2; i >= 0; i--)
+				p.rates[i] = p.rates[i + 1] * 2.0;
+		}
 	}
 
 	j2kcuda_plane planes[J2K_CODEC_MAX_CHANNELS];
@@ -185,7 +243,7 @@ void CudaCodec::WriteFile(OutputFile &file, const FileInfo &info, const Buffer &
 	size_t out_len = 0;
 	Check( j2kcuda_encode(&p, planes, buffer.channels, &out, &out_len) );
 
-	if(info.format == JP2 || info.format == JPX)
+	if(!asWritten && (info.format == JP2 || info.format == JPX))
 	{
 		// JP2 boxes around the codestream (the OpenJPEG path of the reference writes raw J2K only: jp2 is a "TODO" there,
 		// j2k_openjpeg_codec.cpp:613-614; the boxes are those opj_jp2_setup_encoder would produce)

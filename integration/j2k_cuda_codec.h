@@ -28,6 +28,11 @@ class CudaCodec : public Codec
 	virtual void ReadFile(InputFile &file, const Buffer &buffer, unsigned int subsample = 1, Progress *progress = NULL);
 
 	virtual void WriteFile(OutputFile &file, const FileInfo &info, const Buffer &buffer, Progress *progress = NULL);
+
+	// AS_WRITTEN: honour exactly the settings OpenJPEGCodec::WriteFile honours (byte-identical output); FULL: all of them.
+	enum Mode { AS_WRITTEN = 0, FULL = 1 };
+	static void SetMode(Mode m);
+	static Mode GetMode();
 };
 
 }; // namespace j2k

@@ -42,7 +42,8 @@ int j2kcuda_device_count(void) { return j2k::guarded([&]() -> int {
     return n;
 }); }
 
-int j2kcuda_init(int device, j2kcuda_log_fn, void*) { return j2k::guarded([&]() -> int {
+int j2kcuda_init(int device, j2kcuda_log_fn log, void* user) { return j2k::guarded([&]() -> int {
+    j2k::set_log(log, user);
     int n = j2kcuda_device_count();
     if (n == 0) return set_error(J2KCUDA_ERR_NO_DEVICE, "no CUDA device: libj2kcuda has no CPU path");
     if (device >= n) return set_error(J2KCUDA_ERR_PARAM, "device ordinal out of range");
@@ -51,7 +52,7 @@ int j2kcuda_init(int device, j2kcuda_log_fn, void*) { return j2k::guarded([&]() 
     return J2KCUDA_OK;
 }); }
 
-void j2kcuda_shutdown(void) { j2k::out_release_all(); }
+void j2kcuda_shutdown(void) { j2k::encoder_pool_clear(); j2k::decoder_pool_clear(); j2k::out_release_all(); j2k::set_log(nullptr, nullptr); }
 
 int j2kcuda_stage_mct(int32_t* c0, int32_t* c1, int32_t* c2, size_t n, int irreversible, int inverse) { return j2k::guarded([&]() -> int {
     if (!c0 || !c1 || !c2) return set_error(J2KCUDA_ERR_PARAM, "null plane");

@@ -6,7 +6,19 @@
 #include <vector>
 namespace j2k {
 std::string& last_error() { static thread_local std::string e; return e; }
-int set_error(int code, const std::string& msg) { last_error() = msg; return code; }
+namespace {
+std::mutex g_log_mu;
+void (*g_log_fn)(void*, int, const char*) = nullptr;
+void* g_log_user = nullptr;
+}  // namespace
+void set_log(void (*fn)(void*, int, const char*), void* user) { std::lock_guard<std::mutex> g(g_log_mu); g_log_fn = fn; g_log_user = user; }
+void log_msg(int level, const std::string& msg) {
+    void (*fn)(void*, int, const char*); void* user;
+    { std::lock_guard<std::mutex> g(g_log_mu); fn = g_log_fn; user = g_log_user; }
+    if (fn) fn(user, level, msg.c_str());
+}
+int set_error(int code, const std::string& msg) { last_error() = msg; if (code) log_msg(0, msg); return code; }
+bool context_cache_enabled() { static const bool on = [] { const char* e = getenv("J2KCUDA_CONTEXT_CACHE"); return !(e && e[0] == '0'); }(); return on; }
 
 // Output buffers handed to the caller (codestreams, parse tables) and returned through j2kcuda_free().  A frame's
 // codestream is tens of megabytes; a fresh allocation of that size costs more in first-touch page faults than the

@@ -12,6 +12,14 @@ int set_error(int code, const std::string& msg); // stores msg, returns code
 void* out_alloc(size_t n);
 void out_free(void* p);
 void out_release_all();                          // j2kcuda_shutdown
+// j2kcuda_init's log callback: errors (level 0) and notices (level 1) of every entry point go to it
+void set_log(void (*fn)(void*, int, const char*), void* user);
+void log_msg(int level, const std::string& msg);
+// the one-shot calls (j2kcuda_encode / j2kcuda_decode) keep a few contexts between calls, keyed by their parameters:
+// a context for a 4K RGBA16 frame is about 1.5 GB of device and page-locked memory, far too much to allocate per frame
+void encoder_pool_clear();
+void decoder_pool_clear();
+bool context_cache_enabled();
 // No C++ exception may cross the C ABI (a std::bad_alloc from a crafted header used to reach std::terminate):
 // every extern "C" entry point runs its body through this.
 template <class F> inline int guarded(F&& f) noexcept {

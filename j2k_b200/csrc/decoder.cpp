@@ -10,6 +10,7 @@
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 using namespace j2k;
@@ -49,6 +50,7 @@ struct j2kcuda_decoder {
     DwtJob* d_jobs = nullptr; size_t d_jobs_cap = 0;
     uint8_t* d_out = nullptr; size_t d_out_cap = 0;
     uint8_t* h_out = nullptr; size_t h_out_cap = 0;                           // pinned
+    uint8_t* d_stage = nullptr; size_t d_stage_cap = 0;                       // per-channel planes in the caller's sample type
     cudaEvent_t ev[8];
     cudaEvent_t ev_wait = nullptr;   // blocking-sync event: the host worker sleeps instead of spinning
     float ms[8] = {0};
@@ -60,7 +62,7 @@ static void free_decoder(j2kcuda_decoder* d) {
     if (!d) return;
     cudaSetDevice(d->device);
     for (int c = 0; c < 4; ++c) { cudaFree(d->planeA[c]); cudaFree(d->planeB[c]); }
-    cudaFree(d->d_blocks); cudaFree(d->d_seg); cudaFree(d->d_jobs); cudaFree(d->d_out);
+    cudaFree(d->d_blocks); cudaFree(d->d_seg); cudaFree(d->d_jobs); cudaFree(d->d_out); cudaFree(d->d_stage);
     cudaFreeHost(d->h_seg); cudaFreeHost(d->h_out);
     for (auto& e : d->ev) if (e) cudaEventDestroy(e);
     if (d->ev_wait) cudaEventDestroy(d->ev_wait);
@@ -305,7 +307,7 @@ static int download(j2kcuda_decoder* d, const j2kcuda_plane* planes, int nplanes
         const int depth = p.depth ? p.depth : cp.comps[c].prec;
         tight = sb(p.sample_type) == S && (uint8_t*)p.buf == (uint8_t*)planes[0].buf + (size_t)c * S &&
                 p.colbytes == (int64_t)d->ncomp * S && p.rowbytes == (int64_t)d->outW * d->ncomp * S &&
-                (int)p.width == d->outW && (int)p.height == d->outH && depth == cp.comps[c].prec;
+                (int)p.width == d->outW && (int)p.height == d->outH && depth == cp.comps[c].prec && !p.sgnd == !cp.comps[c].sgnd;
     }
     CK(cudaEventRecord(d->ev[7], d->st));
     if (tight) {
@@ -342,23 +344,40 @@ static int download(j2kcuda_decoder* d, const j2kcuda_plane* planes, int nplanes
             CK(stream_wait(d->st, d->ev_wait));
         }
     } else {
-        if (int rc = grow_host(d->h_out, d->h_out_cap, out_bytes)) return rc;
-        CK(cudaMemcpyAsync(d->h_out, d->d_out, out_bytes, cudaMemcpyDeviceToHost, d->st));
-        CK(stream_wait(d->st, d->ev_wait));
+        // Any other destination (other depth, sample type, sign, strides, or fewer channels than components): the
+        // CopyBuffer arithmetic (src/common/j2k_codec.cpp:222-427) runs on the device, one tight plane per channel in the
+        // caller's sample type; the host only moves bytes to the caller's strides.
+        size_t stage = 0;
+        size_t offs[4] = {0, 0, 0, 0};
         for (int c = 0; c < nc; ++c) {
             const j2kcuda_plane& p = planes[c];
-            const int depth = p.depth ? p.depth : cp.comps[c].prec, prec = cp.comps[c].prec, ds = sb(p.sample_type);
-            const int shift = depth - prec;
+            if (p.sample_type > J2KCUDA_INT) return set_error(J2KCUDA_ERR_PARAM, "unknown sample type");
+            const int depth = p.depth ? p.depth : cp.comps[c].prec;
+            if (depth > 8 * sb(p.sample_type)) return set_error(J2KCUDA_ERR_PARAM, "plane depth does not fit its sample type");
+            offs[c] = stage;
+            stage += ((size_t)p.width * p.height * sb(p.sample_type) + 255) & ~(size_t)255;
+        }
+        if (int rc = grow_dev(d->d_stage, d->d_stage_cap, stage)) return rc;
+        if (int rc = grow_host(d->h_out, d->h_out_cap, stage)) return rc;
+        for (int c = 0; c < nc; ++c) {
+            const j2kcuda_plane& p = planes[c];
+            const int depth = p.depth ? p.depth : cp.comps[c].prec;
+            const CopyConv cc = make_copy_conv(J2KCUDA_INT, cp.comps[c].prec, cp.comps[c].sgnd, p.sample_type, depth, p.sgnd);
+            launch_copy_channel(d->d_out, S, d->ncomp, c, cp.comps[0].sgnd, d->outW, (int)p.width, (int)p.height, d->d_stage + offs[c], cc, d->st);
+        }
+        CK(cudaMemcpyAsync(d->h_out, d->d_stage, stage, cudaMemcpyDeviceToHost, d->st));
+        CK(stream_wait(d->st, d->ev_wait));
+        CK(cudaGetLastError());
+        for (int c = 0; c < nc; ++c) {
+            const j2kcuda_plane& p = planes[c];
+            const size_t ds = (size_t)sb(p.sample_type);
             for (uint32_t y = 0; y < p.height; ++y) {
-                const uint8_t* s = d->h_out + ((size_t)y * d->outW * d->ncomp + c) * S;
+                const uint8_t* s = d->h_out + offs[c] + (size_t)y * p.width * ds;
                 uint8_t* q = (uint8_t*)p.buf + (size_t)y * p.rowbytes;
-                for (uint32_t x = 0; x < p.width; ++x, s += (size_t)d->ncomp * S, q += p.colbytes) {
-                    int v = S == 1 ? (cp.comps[c].sgnd ? (int)*(const int8_t*)s : (int)*s)
-                                   : (cp.comps[c].sgnd ? (int)*(const int16_t*)s : (int)*(const uint16_t*)s);
-                    if (shift > 0) v = (v << shift) | (v >> (prec - shift > 0 ? prec - shift : 0));
-                    else if (shift < 0) v >>= -shift;
-                    if (ds == 1) *q = (uint8_t)v; else if (ds == 2) *(uint16_t*)q = (uint16_t)v; else *(int32_t*)q = v;
-                }
+                if (p.colbytes == (int64_t)ds) memcpy(q, s, (size_t)p.width * ds);
+                else if (ds == 1) for (uint32_t x = 0; x < p.width; ++x, q += p.colbytes) *q = s[x];
+                else if (ds == 2) for (uint32_t x = 0; x < p.width; ++x, q += p.colbytes) memcpy(q, s + 2 * (size_t)x, 2);
+                else for (uint32_t x = 0; x < p.width; ++x, q += p.colbytes) memcpy(q, s + 4 * (size_t)x, 4);
             }
         }
     }
@@ -369,6 +388,37 @@ static int download(j2kcuda_decoder* d, const j2kcuda_plane* planes, int nplanes
     d->counters[5] = out_bytes;
     return J2KCUDA_OK;
 }
+
+// ---- decoder contexts kept between one-shot calls (ReadFile after ReadFile); a decoder grows to whatever it is given ----
+namespace {
+std::mutex g_pool_mu;
+std::vector<j2kcuda_decoder*> g_pool;
+constexpr size_t POOL_MAX = 2;
+j2kcuda_decoder* pool_take(int device) {
+    if (!context_cache_enabled()) return nullptr;
+    std::lock_guard<std::mutex> g(g_pool_mu);
+    for (size_t i = 0; i < g_pool.size(); ++i)
+        if (g_pool[i]->device == device) { j2kcuda_decoder* d = g_pool[i]; g_pool.erase(g_pool.begin() + (long)i); return d; }
+    return nullptr;
+}
+void pool_give(j2kcuda_decoder* d) {
+    j2kcuda_decoder* drop = nullptr;
+    if (!context_cache_enabled()) drop = d;
+    else {
+        std::lock_guard<std::mutex> g(g_pool_mu);
+        g_pool.push_back(d);
+        if (g_pool.size() > POOL_MAX) { drop = g_pool.front(); g_pool.erase(g_pool.begin()); }
+    }
+    if (drop) free_decoder(drop);
+}
+}  // namespace
+namespace j2k {
+void decoder_pool_clear() {
+    std::vector<j2kcuda_decoder*> all;
+    { std::lock_guard<std::mutex> g(g_pool_mu); all.swap(g_pool); }
+    for (auto* d : all) free_decoder(d);
+}
+}  // namespace j2k
 
 extern "C" {
 
@@ -431,13 +481,16 @@ int j2kcuda_probe(const uint8_t* bytes, size_t n, j2kcuda_info* out) { return j2
 
 int j2kcuda_decode(const uint8_t* bytes, size_t n, unsigned reduce, const j2kcuda_plane* planes, int nplanes,
                    j2kcuda_abort_fn abort_fn, void* user) { return j2k::guarded([&]() -> int {
-    j2kcuda_decoder* d = j2kcuda_decoder_create(-1);
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return set_error(J2KCUDA_ERR_NO_DEVICE, "no CUDA device: libj2kcuda has no CPU path"); }
+    j2kcuda_decoder* d = pool_take(dev);
+    if (!d) d = j2kcuda_decoder_create(-1);
     if (!d) return J2KCUDA_ERR_NO_DEVICE;
     int rc = j2kcuda_decoder_prepare(d, bytes, n, reduce);
     if (!rc && abort_fn && abort_fn(user)) rc = set_error(J2KCUDA_ERR_ABORTED, "aborted by the caller");
     if (!rc) rc = j2kcuda_decoder_run(d);
     if (!rc) rc = j2kcuda_decoder_download(d, planes, nplanes);
-    j2kcuda_decoder_destroy(d);
+    if (rc == J2KCUDA_ERR_CUDA) j2kcuda_decoder_destroy(d); else pool_give(d);
     return rc;
 }); }
 

@@ -12,6 +12,7 @@
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
+#include "copybuffer.cuh"
 
 namespace j2k {
 
@@ -31,8 +32,7 @@ struct MctParams {
     int irreversible;
     int dc_shift[4];           // 1 << (prec-1) for unsigned components
     int prec[4];
-    int in_shift[4];           // caller depth -> codestream precision (CopyBuffer, j2k_codec.cpp:222-427)
-    int in_depth[4];
+    CopyConv conv[4];          // caller sample -> component sample (CopyBuffer, j2k_codec.cpp:222-427), forward only
 };
 void launch_mct_forward(const PixelSrc& src, const MctParams& mp, int32_t* const planes[4], cudaStream_t st);
 // inverse: planes (int32, or float bit patterns when irreversible) -> caller samples
@@ -44,6 +44,10 @@ struct PixelDst {
     int sgnd;
 };
 void launch_mct_inverse(const PixelDst& dst, const MctParams& mp, const int32_t* const planes[4], cudaStream_t st);
+// decode side of CopyBuffer for a destination that is not the tight image the inverse MCT kernel writes: component c of
+// the tight interleaved image `img` (S-byte samples, signed when sgnd) -> a tight w x h plane of the caller's sample type
+void launch_copy_channel(const uint8_t* img, int S, int ncomp, int c, int sgnd, int img_w, int w, int h, uint8_t* dst,
+                         const CopyConv& conv, cudaStream_t st);
 // bare three-plane transforms used by the stage entry points (mct.cpp:94-471)
 void launch_mct_planes(int32_t* c0, int32_t* c1, int32_t* c2, size_t n, int irreversible, int inverse, cudaStream_t st);
 

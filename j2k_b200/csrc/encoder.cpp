@@ -13,6 +13,7 @@
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 using namespace j2k;
@@ -241,7 +242,9 @@ static int upload_planes(j2kcuda_encoder* e, const j2kcuda_plane* planes, int np
         if (!pl.buf || (int)pl.width != e->W || (int)pl.height != e->H)
             return set_error(J2KCUDA_ERR_PARAM, "plane size differs from the image size");
         if (sample_bytes_of(pl.sample_type) != S || pl.colbytes < S || pl.rowbytes < 0)
-            return set_error(J2KCUDA_ERR_PARAM, "planes must share one sample type and have positive strides");
+            return set_error(J2KCUDA_ERR_PARAM, "planes must share one sample size and have positive strides");
+        if (pl.sample_type > J2KCUDA_INT || pl.depth > 8 * S)
+            return set_error(J2KCUDA_ERR_PARAM, "plane depth does not fit its sample type");
         const uint8_t* lo = (const uint8_t*)pl.buf + (size_t)e->row0 * pl.rowbytes;     // only the rows of this context's tiles
         const uint8_t* hi = (const uint8_t*)pl.buf + (size_t)(e->row1 - 1) * pl.rowbytes + (size_t)(e->W - 1) * pl.colbytes + S;
         ranges.push_back({lo, hi, 0});
@@ -310,7 +313,7 @@ static int upload_planes(j2kcuda_encoder* e, const j2kcuda_plane* planes, int np
     }
     memset(&e->src, 0, sizeof(e->src));
     e->src.sample_bytes = S;
-    e->src.sgnd = planes[0].sgnd;
+    e->src.sgnd = 0;                                   // sign handling lives in mp.conv (copybuffer.cuh)
     for (int c = 0; c < e->ncomp; ++c) {
         const uint8_t* lo = (const uint8_t*)planes[c].buf + (size_t)e->row0 * planes[c].rowbytes;
         for (auto& m : merged)          // base = where row 0 would be (rows above row0 are never touched)
@@ -318,13 +321,45 @@ static int upload_planes(j2kcuda_encoder* e, const j2kcuda_plane* planes, int np
         e->src.colbytes[c] = planes[c].colbytes;
         e->src.rowbytes[c] = planes[c].rowbytes;
         const int depth = planes[c].depth ? planes[c].depth : e->mp.prec[c];
-        e->mp.in_depth[c] = depth;
-        e->mp.in_shift[c] = e->mp.prec[c] - depth;
+        e->mp.conv[c] = make_copy_conv(planes[c].sample_type, depth, planes[c].sgnd, J2KCUDA_INT, e->mp.prec[c], (int)e->p.sgnd);
     }
     e->counters[4] = h2d;
     e->have_input = true;
     return J2KCUDA_OK;
 }
+
+// ---- contexts kept between one-shot calls (WriteFile after WriteFile with the same settings) ----
+namespace {
+std::mutex g_pool_mu;
+std::vector<j2kcuda_encoder*> g_pool;
+constexpr size_t POOL_MAX = 2;
+j2kcuda_encoder* pool_take(const j2kcuda_params& p) {
+    if (!context_cache_enabled()) return nullptr;
+    int cur = 0;
+    if (p.device < 0 && cudaGetDevice(&cur) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    std::lock_guard<std::mutex> g(g_pool_mu);
+    for (size_t i = 0; i < g_pool.size(); ++i)
+        if (memcmp(&g_pool[i]->p, &p, sizeof(p)) == 0 && (p.device >= 0 || g_pool[i]->device == cur)) { j2kcuda_encoder* e = g_pool[i]; g_pool.erase(g_pool.begin() + (long)i); return e; }
+    return nullptr;
+}
+void pool_give(j2kcuda_encoder* e) {
+    j2kcuda_encoder* drop = nullptr;
+    if (!context_cache_enabled()) drop = e;
+    else {
+        std::lock_guard<std::mutex> g(g_pool_mu);
+        g_pool.push_back(e);
+        if (g_pool.size() > POOL_MAX) { drop = g_pool.front(); g_pool.erase(g_pool.begin()); }
+    }
+    if (drop) free_encoder(drop);
+}
+}  // namespace
+namespace j2k {
+void encoder_pool_clear() {
+    std::vector<j2kcuda_encoder*> all;
+    { std::lock_guard<std::mutex> g(g_pool_mu); all.swap(g_pool); }
+    for (auto* e : all) free_encoder(e);
+}
+}  // namespace j2k
 
 extern "C" {
 
@@ -354,13 +389,12 @@ int j2kcuda_encoder_set_device_input(j2kcuda_encoder* e, const void* d_pixels, i
     const int S = sample_bytes_of(sample_type);
     memset(&e->src, 0, sizeof(e->src));
     e->src.sample_bytes = S;
-    e->src.sgnd = (int)e->p.sgnd;
+    e->src.sgnd = 0;
     for (int c = 0; c < e->ncomp; ++c) {
         e->src.base[c] = (const uint8_t*)d_pixels + (size_t)c * S;
         e->src.colbytes[c] = (int64_t)e->ncomp * S;
         e->src.rowbytes[c] = pitch_bytes;
-        e->mp.in_depth[c] = e->mp.prec[c];
-        e->mp.in_shift[c] = 0;
+        e->mp.conv[c] = make_copy_conv(sample_type, e->mp.prec[c], (int)e->p.sgnd, J2KCUDA_INT, e->mp.prec[c], (int)e->p.sgnd);
     }
     CK(cudaSetDevice(e->device));
     CK(cudaEventRecord(e->ev[8], e->st));
@@ -503,12 +537,14 @@ int j2kcuda_encoder_counters(j2kcuda_encoder* e, uint64_t* v, int n) { return j2
 }); }
 
 int j2kcuda_encode(const j2kcuda_params* p, const j2kcuda_plane* planes, int nplanes, uint8_t** out, size_t* out_len) { return j2k::guarded([&]() -> int {
-    j2kcuda_encoder* e = j2kcuda_encoder_create(p);
+    if (!p) return set_error(J2KCUDA_ERR_PARAM, "null params");
+    j2kcuda_encoder* e = pool_take(*p);
+    if (!e) e = j2kcuda_encoder_create(p);
     if (!e) return J2KCUDA_ERR_PARAM;
     int rc = j2kcuda_encoder_upload(e, planes, nplanes);
     if (!rc) rc = j2kcuda_encoder_run(e);
     if (!rc) rc = j2kcuda_encoder_finish(e, out, out_len);
-    j2kcuda_encoder_destroy(e);
+    if (rc) j2kcuda_encoder_destroy(e); else pool_give(e);
     return rc;
 }); }
 

@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(256) k_mct_forward(const FwdArgs a) {
             for (int k = 0; k < 4; ++k) {
                 int ch[4];
 #pragma unroll
-                for (int j = 0; j < (NCH > 0 ? NCH : 1); ++j) ch[j] = word_sample<S>(w, k * NCH + j, a.src.sgnd);
+                for (int j = 0; j < (NCH > 0 ? NCH : 1); ++j) ch[j] = word_sample<S>(w, k * NCH + j, 0);
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
                     int sel = a.chan[c];
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(256) k_mct_forward(const FwdArgs a) {
                 if (c >= a.mp.ncomp) continue;
                 const uint8_t* p = a.src.base[c] + (long long)y * a.src.rowbytes[c] + (long long)x * a.src.colbytes[c];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) v[c][k] = k < nv ? load_sample<S>(p + (long long)k * a.src.colbytes[c], a.src.sgnd) : 0;
+                for (int k = 0; k < 4; ++k) v[c][k] = k < nv ? load_sample<S>(p + (long long)k * a.src.colbytes[c], 0) : 0;
             }
         }
 #pragma unroll
@@ -116,8 +116,7 @@ __global__ void __launch_bounds__(256) k_mct_forward(const FwdArgs a) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 int s = v[c][k];
-                if (a.mp.in_shift[c] > 0) s = (s << a.mp.in_shift[c]) | (s >> (a.mp.in_depth[c] - a.mp.in_shift[c]));
-                else if (a.mp.in_shift[c] < 0) s >>= -a.mp.in_shift[c];
+                if (!a.mp.conv[c].plain) s = (int)copy_convert(a.mp.conv[c].src_type == 2 ? (long long)(uint32_t)s : (long long)s, a.mp.conv[c]);
                 s -= a.mp.dc_shift[c];
                 v[c][k] = a.mp.irreversible ? s << 11 : s;
             }
@@ -179,11 +178,7 @@ __global__ void __launch_bounds__(256) k_mct_inverse(const InvArgs a) {
             const int hi = a.dst.sgnd ? (1 << (a.mp.prec[c] - 1)) - 1 : (1 << a.mp.prec[c]) - 1;
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                int s = min(max(v[c][k] + a.mp.dc_shift[c], lo), hi);
-                // codestream precision -> caller depth (CopyBuffer, j2k_codec.cpp:222-427)
-                if (a.mp.in_shift[c] > 0) s >>= a.mp.in_shift[c];
-                else if (a.mp.in_shift[c] < 0) s = (s << -a.mp.in_shift[c]) | (s >> (a.mp.prec[c] + a.mp.in_shift[c]));
-                v[c][k] = s;
+                v[c][k] = min(max(v[c][k] + a.mp.dc_shift[c], lo), hi);
             }
         }
         if (NCH > 0 && nv == 4) {
@@ -223,6 +218,21 @@ __global__ void __launch_bounds__(256) k_mct_inverse(const InvArgs a) {
                 for (int k = 0; k < nv; ++k) store_sample<S>(p + (long long)k * a.dst.colbytes[c], v[c][k]);
             }
         }
+    }
+}
+
+__global__ void __launch_bounds__(256) k_copy_channel(const uint8_t* __restrict__ img, int S, int ncomp, int c, int sgnd, int img_w, int w, int h,
+                                                      uint8_t* __restrict__ dst, const CopyConv cc) {
+    const long long total = (long long)w * h;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int y = (int)(i / w), x = (int)(i % w);
+        const uint8_t* p = img + (((long long)y * img_w + x) * ncomp + c) * S;
+        long long s = S == 1 ? (sgnd ? (long long)*reinterpret_cast<const int8_t*>(p) : (long long)*p)
+                             : (sgnd ? (long long)*reinterpret_cast<const int16_t*>(p) : (long long)*reinterpret_cast<const uint16_t*>(p));
+        const long long r = cc.plain ? s : copy_convert(s, cc);
+        if (cc.dst_type == 0) dst[i] = (uint8_t)r;
+        else if (cc.dst_type == 1) reinterpret_cast<uint16_t*>(dst)[i] = (uint16_t)r;
+        else reinterpret_cast<uint32_t*>(dst)[i] = (uint32_t)r;
     }
 }
 
@@ -301,6 +311,12 @@ void launch_mct_inverse(const PixelDst& dst, const MctParams& mp, const int32_t*
     if (a.nch) { uint8_t* lo = dst.base[0]; for (int c = 1; c < mp.ncomp; ++c) if (dst.base[c] < lo) lo = dst.base[c]; a.dst.base[0] = lo; }
     int grid = grid_for((long long)((mp.width + 3) / 4) * mp.height);
     MCT_DISPATCH(k_mct_inverse, a, dst.sample_bytes, a.nch, grid, st);
+}
+
+void launch_copy_channel(const uint8_t* img, int S, int ncomp, int c, int sgnd, int img_w, int w, int h, uint8_t* dst,
+                         const CopyConv& conv, cudaStream_t st) {
+    if (w <= 0 || h <= 0) return;
+    k_copy_channel<<<grid_for((long long)w * h), 256, 0, st>>>(img, S, ncomp, c, sgnd, img_w, w, h, dst, conv);
 }
 
 void launch_mct_planes(int32_t* c0, int32_t* c1, int32_t* c2, size_t n, int irreversible, int inverse, cudaStream_t st) {

@@ -32,3 +32,11 @@ extern "C" int t1dec_host_block(const uint8_t* data, int len, int w, int h, int 
     decode_block(b, R, cb, st, zc9, sc2, tab, seg.data(), 1, 0, 1);
     return 0;
 }
+
+// ---- the sample conversion the MCT kernels run (j2k_b200/csrc/copybuffer.cuh), compiled for the host ----
+#include "../../j2k_b200/csrc/copybuffer.cuh"
+extern "C" void copyconv_host(const int64_t* src, int64_t* dst, int n, int src_type, int src_depth, int src_sgnd, int dst_type,
+                              int dst_depth, int dst_sgnd) {
+    const j2k::CopyConv c = j2k::make_copy_conv(src_type, src_depth, src_sgnd, dst_type, dst_depth, dst_sgnd);
+    for (int i = 0; i < n; ++i) dst[i] = c.plain ? j2k::cb_as(dst_type, src[i]) : j2k::copy_convert(src[i], c);
+}
