@@ -54,7 +54,8 @@ enum { J2KCUDA_LRCP = 0, J2KCUDA_RLCP = 1, J2KCUDA_RPCL = 2, J2KCUDA_PCRL = 3, J
 /* rsiz profiles, openjpeg.h:225-226 */
 enum { J2KCUDA_PROFILE_NONE = 0, J2KCUDA_PROFILE_CINEMA_2K = 3, J2KCUDA_PROFILE_CINEMA_4K = 4 };
 /* Which encoder's Tier-2 policy to reproduce byte for byte. */
-enum { J2KCUDA_COMPAT_GROK_2_1_1 = 0, J2KCUDA_COMPAT_OPENJPEG_2_5 = 1 };
+enum { J2KCUDA_COMPAT_GROK_2_1_1 = 0, J2KCUDA_COMPAT_OPENJPEG_2_5 = 1 /* COM text of 2.5.4 (Pillow's) */,
+       J2KCUDA_COMPAT_OPENJPEG_2_5_3 = 2 /* same policy, COM text of 2.5.3 (OpenCV's) */ };
 
 /* Encoder parameters: the subset of opj_cparameters_t (openjpeg.h:356-486) the plug-in and the
  * BASELINE configs use; zero means "library default" (openjpeg.cpp:706-728). */

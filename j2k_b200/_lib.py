@@ -10,7 +10,7 @@ OK, ERR_PARAM, ERR_NO_DEVICE, ERR_CUDA, ERR_STREAM, ERR_NOMEM, ERR_ABORTED, ERR_
 UCHAR, USHORT, UINT, INT = range(4)
 LRCP, RLCP, RPCL, PCRL, CPRL = range(5)
 PROFILE_NONE, PROFILE_CINEMA_2K, PROFILE_CINEMA_4K = 0, 3, 4
-COMPAT_GROK, COMPAT_OPENJPEG = 0, 1
+COMPAT_GROK, COMPAT_OPENJPEG, COMPAT_OPENJPEG_253 = 0, 1, 2
 
 
 class Plane(C.Structure):

@@ -15,6 +15,7 @@ namespace j2k {
 
 static const char* kCommentGrok = "Created by Grok     version 2.1.1";
 static const char* kCommentOpj25 = "Created by OpenJPEG version 2.5.4";
+static const char* kCommentOpj253 = "Created by OpenJPEG version 2.5.3";
 
 // What the reference refuses before it encodes (opj_compress parameter checks and opj_j2k_encoding_validation,
 // j2k.cpp:6640-6680), plus the limits of this library.  nullptr = fine.
@@ -114,7 +115,7 @@ void setup_coding_params(const ::j2kcuda_params& p, CodingParams& cp) {
     cp.csty = csty;
     cp.prog = prog;
     cp.mct = (mct && cp.ncomp >= 3) ? 1 : 0;
-    cp.comment = cp.compat == J2KCUDA_COMPAT_OPENJPEG_2_5 ? kCommentOpj25 : kCommentGrok;
+    cp.comment = cp.compat == J2KCUDA_COMPAT_OPENJPEG_2_5 ? kCommentOpj25 : (cp.compat == J2KCUDA_COMPAT_OPENJPEG_2_5_3 ? kCommentOpj253 : kCommentGrok);
     for (int c = 0; c < cp.ncomp; ++c) {
         CompParams& t = cp.comps[c];
         t.prec = (int)p.prec; t.sgnd = p.sgnd ? 1 : 0; t.dx = t.dy = 1;
@@ -496,7 +497,7 @@ static void pcrd_bisect(const CodingParams& cp, EncTile& t, const std::vector<Ti
             goodthresh = (hi == 0) ? thresh : hi;
         } else {
             goodthresh = min_slope;
-            all = cp.compat == J2KCUDA_COMPAT_OPENJPEG_2_5;
+            all = cp.compat == J2KCUDA_COMPAT_OPENJPEG_2_5 || cp.compat == J2KCUDA_COMPAT_OPENJPEG_2_5_3;
         }
         makelayer(cp, t, layno, goodthresh, true, all);
     }

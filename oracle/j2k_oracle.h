@@ -6,7 +6,8 @@
  * mqc.cpp).  Written from the algorithm, not from the reference's code layout: per-sample state
  * arrays instead of packed flag words, absolute-coordinate lifting instead of interleave buffers.
  * Parity pinned differentially against oracle/_ref/libgrokref.so (the reference compiled here)
- * and against the fixtures in tests/golden/ (tests/test_oracle_vs_ref.py, tests/test_golden.py).
+ * and against the fixtures in tests/golden/ (written by tests/golden/make_golden.py from the compiled reference and
+ * OpenJPEG 2.5.x; tests/test_oracle_vs_ref.py, tests/test_golden.py).
  */
 #ifndef J2K_ORACLE_H
 #define J2K_ORACLE_H

@@ -81,6 +81,13 @@ void ref_set_verbose(int v) { g_verbose = v; }
 static int g_jp2 = 0, g_alpha = -1;
 void ref_set_jp2(int on, int alpha_comp) { g_jp2 = on; g_alpha = alpha_comp; }
 const char* ref_version(void) { return opj_version(); }
+/* Extra encoder switches for the next ref_encode calls: code-block style (opj_cparameters_t::mode: 1 LAZY, 2 RESET,
+ * 4 TERMALL, 8 VSC, 16 PTERM, 32 SEGSYM; j2k.h:77-82), region of interest (component, up-shift), SOP / EPH markers (csty 2 / 4),
+ * sub-sampling of components 1.. (dx, dy; component 0 stays 1x1). */
+static int g_mode = 0, g_roi_comp = -1, g_roi_shift = 0, g_csty = 0, g_sub_dx = 1, g_sub_dy = 1;
+void ref_set_extra(int mode, int roi_comp, int roi_shift, int csty, int sub_dx, int sub_dy) {
+    g_mode = mode; g_roi_comp = roi_comp; g_roi_shift = roi_shift; g_csty = csty; g_sub_dx = sub_dx > 0 ? sub_dx : 1; g_sub_dy = sub_dy > 0 ? sub_dy : 1;
+}
 
 /* Whole-frame encode through grok's public API.  planes[c] = w*h int32 samples (unsigned
  * values, as CopyBuffer would leave them).  Returns 0 on success. */
@@ -91,13 +98,14 @@ int ref_encode(const int32_t* const* planes, int ncomp, int w, int h, int prec, 
     opj_image_cmptparm_t cp[8];
     memset(cp, 0, sizeof(cp));
     for (int i = 0; i < ncomp; ++i) {
-        cp[i].dx = cp[i].dy = 1; cp[i].w = w; cp[i].h = h; cp[i].prec = prec;
+        cp[i].dx = i ? g_sub_dx : 1; cp[i].dy = i ? g_sub_dy : 1;
+        cp[i].w = (w + cp[i].dx - 1) / cp[i].dx; cp[i].h = (h + cp[i].dy - 1) / cp[i].dy; cp[i].prec = prec;
         cp[i].bpp = prec; cp[i].sgnd = sgnd;
     }
     opj_image_t* image = opj_image_create(ncomp, cp, ncomp >= 3 ? OPJ_CLRSPC_SRGB : OPJ_CLRSPC_GRAY);
     if (!image) return 1;
     image->x0 = image->y0 = 0; image->x1 = w; image->y1 = h;
-    for (int i = 0; i < ncomp; ++i) memcpy(image->comps[i].data, planes[i], sizeof(int32_t) * (size_t)w * h);
+    for (int i = 0; i < ncomp; ++i) memcpy(image->comps[i].data, planes[i], sizeof(int32_t) * (size_t)cp[i].w * cp[i].h);
     if (g_jp2 && g_alpha >= 0 && g_alpha < ncomp) image->comps[g_alpha].alpha = 1;
 
     opj_cparameters_t params;
@@ -121,6 +129,9 @@ int ref_encode(const int32_t* const* planes, int ncomp, int w, int h, int prec, 
         params.max_cs_size = p->max_cs_size;
     }
     params.numThreads = p->num_threads > 0 ? p->num_threads : 1;
+    params.mode = g_mode;
+    params.csty |= g_csty;
+    if (g_roi_comp >= 0) { params.roi_compno = g_roi_comp; params.roi_shift = g_roi_shift; }
 
     int rc = 2;
     MemOut mo;
@@ -150,7 +161,10 @@ int ref_encode(const int32_t* const* planes, int ncomp, int w, int h, int prec, 
     return rc;
 }
 
-/* Whole-stream decode.  planes[c] must hold w*h int32 (caller sized them from ref_probe). */
+static int g_last_dx = 1, g_last_dy = 1;
+void ref_last_subsampling(int* dx, int* dy) { *dx = g_last_dx; *dy = g_last_dy; }   /* of component 1 in the last header read */
+/* Whole-stream decode.  planes[c] must hold w*h int32 (caller sized them from ref_probe; sub-sampled components hold
+ * ceil(w / dx) * ceil(h / dy)). */
 int ref_decode(const uint8_t* data, size_t len, int reduce, int nthreads,
                int32_t* const* planes, int max_planes, int* info /* w,h,ncomp,prec,sgnd */)
 {
@@ -171,6 +185,7 @@ int ref_decode(const uint8_t* data, size_t len, int reduce, int nthreads,
         if (opj_setup_decoder(codec, &dp) && opj_read_header(stream, codec, &image)) {
             info[0] = image->comps[0].w; info[1] = image->comps[0].h; info[2] = image->numcomps;
             info[3] = image->comps[0].prec; info[4] = image->comps[0].sgnd;
+            g_last_dx = image->numcomps > 1 ? image->comps[1].dx : 1; g_last_dy = image->numcomps > 1 ? image->comps[1].dy : 1;
             if (!planes) rc = 0;
             else if (opj_decode(codec, stream, image) && opj_end_decompress(codec, stream)) {
                 rc = 0;
@@ -291,6 +306,74 @@ int ref_t1_encode_cblk(const int32_t* coeff, int w, int h, int stride, int orien
     if (total > cap) { opj_t1_opt_destroy(t1); return 2; }
     memcpy(out, cblk.data, total);
     opj_t1_opt_destroy(t1);
+    return 0;
+}
+
+/* One code-block through the reference's generic decoder (t1.cpp:1337-1448): `data` = the block's bytes, made of nsegs
+ * segments (seg_len bytes, seg_passes passes each; with cblksty 0 there is one).  out = w*h values in the decoder's
+ * representation (one extra fractional bit), before the ROI down-shift and dequantisation of T1Decoder.cpp:59-99. */
+int ref_t1_decode_cblk(const uint8_t* data, const int* seg_len, const int* seg_passes, int nsegs, int w, int h, int orient,
+                       int numbps, int roishift, int cblksty, int32_t* out)
+{
+    opj_t1_t* t1 = opj_t1_create(false, (uint16_t)w, (uint16_t)h);
+    if (!t1) return 1;
+    opj_tcd_cblk_dec_t cblk;
+    memset(&cblk, 0, sizeof(cblk));
+    opj_vec_init(&cblk.seg_buffers, true);
+    std::vector<opj_tcd_seg_t> segs(nsegs > 0 ? nsegs : 1);
+    memset(segs.data(), 0, sizeof(opj_tcd_seg_t) * segs.size());
+    size_t pos = 0;
+    for (int i = 0; i < nsegs; ++i) {
+        segs[i].dataindex = (uint32_t)pos; segs[i].len = seg_len[i];
+        segs[i].numpasses = segs[i].real_num_passes = seg_passes[i]; segs[i].maxpasses = 109;
+        pos += seg_len[i];
+    }
+    /* one buffer for the whole block keeps opj_min_buf's 16-bit lengths out of the way for blocks beyond 64 KB */
+    if (pos) opj_min_buf_vec_push_back(&cblk.seg_buffers, (uint8_t*)data, (uint16_t)(pos > 65535 ? 65535 : pos));
+    cblk.segs = segs.data();
+    cblk.x0 = 0; cblk.y0 = 0; cblk.x1 = w; cblk.y1 = h;
+    cblk.numbps = numbps; cblk.numsegs = cblk.real_num_segs = nsegs;
+    memset(out, 0, sizeof(int32_t) * (size_t)w * h);
+    bool ok = pos <= 65535 && opj_t1_decode_cblk(t1, &cblk, orient, roishift, cblksty);
+    if (ok && pos) memcpy(out, t1->data, sizeof(int32_t) * (size_t)w * h);      /* the decoder's block buffer is contiguous (T1Decoder.cpp:77-99) */
+    opj_vec_cleanup(&cblk.seg_buffers);
+    opj_t1_destroy(t1);
+    return ok ? 0 : 2;
+}
+
+/* One code-block through the reference's GENERIC encoder (t1.cpp:1537-1673; the one used when cblksty != 0): quantised like
+ * ref_t1_encode_cblk.  Outputs per pass: cumulative rate, length and term flag; the bytes. */
+int ref_t1_encode_cblk_generic(const int32_t* coeff, int w, int h, int stride, int orient, int cblksty, uint8_t* out, int cap,
+                               int* numbps, int* npasses, int* rates, int* lens, int* terms)
+{
+    opj_t1_t* t1 = opj_t1_create(true, 0, 0);
+    if (!t1 || !opj_t1_allocate_buffers(t1, w, h)) return 1;
+    t1->data_stride = w;                                  /* encoder layout, t1.cpp:1496 */
+    uint32_t max = 0;
+    for (int j = 0; j < h; ++j)
+        for (int i = 0; i < w; ++i) {
+            int32_t tmp = coeff[j * stride + i] * (1 << T1_NMSEDEC_FRACBITS);
+            t1->data[j * w + i] = tmp;
+            uint32_t mag = (uint32_t)opj_int_abs(tmp);
+            if (mag > max) max = mag;
+        }
+    opj_tcd_cblk_enc_t cblk;
+    memset(&cblk, 0, sizeof(cblk));
+    std::vector<uint8_t> data((size_t)w * h * 8 + 64);
+    std::vector<opj_tcd_pass_t> passes(110);
+    cblk.data = data.data() + 1;
+    cblk.passes = passes.data();
+    cblk.x0 = 0; cblk.y0 = 0; cblk.x1 = w; cblk.y1 = h;
+    opj_t1_encode_cblk(t1, &cblk, orient, 0, 0, 1, 1.0, cblksty, 1, NULL, 0);
+    *numbps = cblk.numbps; *npasses = cblk.totalpasses;
+    int total = 0;
+    for (uint32_t i = 0; i < cblk.totalpasses; ++i) {
+        rates[i] = passes[i].rate; lens[i] = passes[i].len; terms[i] = passes[i].term;
+        total = passes[i].rate;
+    }
+    if (total > cap) { opj_t1_destroy(t1); return 2; }
+    memcpy(out, cblk.data, total);
+    opj_t1_destroy(t1);
     return 0;
 }
 

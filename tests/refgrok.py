@@ -133,3 +133,39 @@ def mct(c0, c1, c2, inverse=False, real=False):
     getattr(lib(), fn)(C.c_void_p(a[0].ctypes.data), C.c_void_p(a[1].ctypes.data),
                        C.c_void_p(a[2].ctypes.data), C.c_uint64(a[0].size))
     return a
+
+
+def set_extra(mode=0, roi_comp=-1, roi_shift=0, csty=0, sub=(1, 1)):
+    """switches for the next encode() calls: code-block style bits (1 LAZY 2 RESET 4 TERMALL 8 VSC 16 PTERM 32 SEGSYM),
+    region of interest, SOP (csty 2) / EPH (csty 4) markers, sub-sampling of components 1.."""
+    lib().ref_set_extra(mode, roi_comp, roi_shift, csty, sub[0], sub[1])
+
+
+def t1_decode_cblk(data, w, h, orient, numbps, segs, cblksty=0, roishift=0):
+    """segs: list of (length, passes) -> (h, w) int32 in the decoder's representation (one extra fractional bit)"""
+    buf = np.frombuffer(bytes(data) + b"\0" * 8, dtype=np.uint8).copy()
+    sl = (C.c_int * len(segs))(*[s[0] for s in segs])
+    sp = (C.c_int * len(segs))(*[s[1] for s in segs])
+    out = np.zeros((h, w), dtype=np.int32)
+    rc = lib().ref_t1_decode_cblk(C.c_void_p(buf.ctypes.data), sl, sp, len(segs), w, h, orient, numbps, roishift, cblksty,
+                                  C.c_void_p(out.ctypes.data))
+    if rc != 0:
+        raise RuntimeError("ref_t1_decode_cblk rc=%d" % rc)
+    return out
+
+
+def t1_encode_cblk_generic(coeff, orient, cblksty):
+    """the reference's generic encoder (used when cblksty != 0) -> bytes, numbps, per pass (rate, len, term)"""
+    coeff = np.ascontiguousarray(coeff, dtype=np.int32)
+    h, w = coeff.shape
+    out = np.empty(w * h * 8 + 64, dtype=np.uint8)
+    numbps = C.c_int(0); npasses = C.c_int(0)
+    rates = (C.c_int * 128)(); lens = (C.c_int * 128)(); terms = (C.c_int * 128)()
+    rc = lib().ref_t1_encode_cblk_generic(C.c_void_p(coeff.ctypes.data), w, h, w, orient, cblksty, C.c_void_p(out.ctypes.data), out.size,
+                                          C.byref(numbps), C.byref(npasses), rates, lens, terms)
+    if rc != 0:
+        raise RuntimeError("ref_t1_encode_cblk_generic rc=%d" % rc)
+    n = npasses.value
+    total = rates[n - 1] if n else 0
+    return dict(data=out[:total].tobytes(), numbps=numbps.value, npasses=n, rates=[rates[i] for i in range(n)],
+                lens=[lens[i] for i in range(n)], terms=[terms[i] for i in range(n)])

@@ -70,3 +70,39 @@ def test_16_bit_through_opencv(nc):
     back = cv2.imdecode(np.frombuffer(ours, np.uint8), cv2.IMREAD_UNCHANGED)
     assert back is not None and back.dtype == np.uint16
     assert np.array_equal(back[..., order], img)
+
+
+# ---- 16-bit byte identity with a real OpenJPEG (row N1): OpenCV's embedded libopenjp2 2.5.3 writes lossless 5/3, 6 resolutions,
+# 64x64 code-blocks, LRCP, one layer, NO multi-component transform, inside a JP2 wrapper; its jp2c payload is the codestream ----
+def opencv_codestream(img):
+    cv2 = pytest.importorskip("cv2")
+    import ctypes as C
+    ok, enc = cv2.imencode(".jp2", img, [cv2.IMWRITE_JPEG2000_COMPRESSION_X1000, 1000])
+    assert ok
+    b = enc.tobytes()
+    info = L.Info()
+    assert L.lib().j2kcuda_probe(b, C.c_size_t(len(b)), C.byref(info)) == 0, L.last_error()      # host-only call
+    assert info.is_jp2 and info.mct == 0 and info.numresolution == 6 and info.numlayers == 1 and info.prec[0] == 16
+    return b[info.codestream_offset:info.codestream_offset + info.codestream_length]
+
+
+@pytest.mark.parametrize("h,w,nc,kind", [(270, 480, 3, "smooth"), (270, 480, 4, "smooth"), (135, 211, 3, "noise"), (97, 64, 4, "ramp")])
+def test_host_tier2_writes_openjpeg_2_5_3_bytes_for_16_bit(h, w, nc, kind):
+    img = make_frame(h, w, nc, 16, kind, seed=3)
+    ref = opencv_codestream(img)
+    order = [2, 1, 0, 3][:nc]                                        # OpenCV's arrays are B, G, R(, A); the file's components R, G, B(, A)
+    p = L.default_params(width=w, height=h, ncomp=nc, prec=16, mct=0, compat=L.COMPAT_OPENJPEG_253)
+    assert hostpipe.encode([img[..., c].astype(np.int32) for c in order], 16, p) == ref
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("h,w,nc", [(270, 480, 3), (270, 480, 4), (2160, 4096, 3), (2160, 4096, 4)])
+def test_cuda_16_bit_codestream_is_byte_identical_to_openjpeg_2_5_3(h, w, nc):
+    """north_star: "4K 16-bit RGB lossless encode ... byte-exact with OpenJPEG" -- against the OpenJPEG that can run here"""
+    import j2k
+    img = make_frame(h, w, nc, 16, "smooth", seed=11)
+    ref = opencv_codestream(img)
+    order = [2, 1, 0, 3][:nc]
+    ours = j2k.encode(np.ascontiguousarray(img[..., order]), 16, mct=0, compat=L.COMPAT_OPENJPEG_253)
+    assert ours == ref
+    assert np.array_equal(j2k.decode(ref)[..., order], img)          # and its stream through our decoder, bit-exact
