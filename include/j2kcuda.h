@@ -189,6 +189,26 @@ int j2kcuda_encode_batch(const j2kcuda_params* p, const j2kcuda_plane* const* fr
 int j2kcuda_decode_batch(const uint8_t* const* streams, const size_t* lens, int nframes,
                          unsigned reduce, const j2kcuda_plane* const* frames, int nplanes);
 
+/* ---- several GPUs behind one call (device assignment inside the library; 8e: the path shards with no
+ *      exchange step, so no collective is involved).  For a C++ host such as the plug-in; bench.py uses one process
+ *      per GPU instead. ---------------------------------------------------------------------------------------- */
+/* Frames of a sequence over `ndevices` GPUs: `workers_per_device` contexts on each, all pulling frames from one shared
+ * counter.  Use with j2kcuda_sequence_encode / _decode / _stats / _destroy (host frames; the DEVICE_PIXELS flag is
+ * for single-device sequences). */
+j2kcuda_sequence* j2kcuda_sequence_create_multi(const j2kcuda_params* p, const int* devices, int ndevices,
+                                                int workers_per_device);
+/* Tiles of ONE very large frame over several GPUs (config C4): device k encodes / decodes a contiguous run of tiles
+ * with its own context and host thread; encode concatenates the tile-part fragments behind one main header (the
+ * result is byte-identical to a one-device encode), decode routes tile-parts by their SOT tile index
+ * (j2k.cpp:9247-9333) and every device writes its tiles' rectangles into the caller's image (which must have the
+ * codestream's own sample layout: interleaved, same sample size and depth).  p may be NULL for decode only. */
+typedef struct j2kcuda_tiles j2kcuda_tiles;
+j2kcuda_tiles* j2kcuda_tiles_create(const j2kcuda_params* p, const int* devices, int ndevices);
+void j2kcuda_tiles_destroy(j2kcuda_tiles* t);
+int j2kcuda_tiles_encode(j2kcuda_tiles* t, const j2kcuda_plane* planes, int nplanes, uint8_t** out, size_t* out_len);
+int j2kcuda_tiles_decode(j2kcuda_tiles* t, const uint8_t* bytes, size_t n, unsigned reduce,
+                         const j2kcuda_plane* planes, int nplanes);
+
 /* ---- one frame whose tiles were encoded on several GPUs ----------------------------------- */
 /* p describes the whole frame (tile_count ignored).  frags[i] are the fragments returned by encoders
  * created with tile ranges that together cover every tile exactly once, in any order; the result

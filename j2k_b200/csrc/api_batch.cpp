@@ -19,6 +19,7 @@ using namespace j2k;
 struct j2kcuda_sequence {
     int device = -1;
     int nworkers = 0;
+    std::vector<int> devs;            // device of worker w (one entry per worker; all equal for a single-GPU sequence)
     bool have_params = false;
     j2kcuda_params params;
     std::vector<j2kcuda_encoder*> enc;
@@ -82,8 +83,28 @@ j2kcuda_sequence* j2kcuda_sequence_create(const j2kcuda_params* p, int device, i
         if (device >= 0) s->params.device = device;
         else s->device = p->device;
     }
+    s->devs.assign((size_t)nworkers, s->device);
     return s;
 } catch (...) { set_error(J2KCUDA_ERR_NOMEM, "j2kcuda_sequence_create: out of memory or internal error"); return nullptr; } }
+
+// Frames of a sequence over SEVERAL GPUs of the box from one process (what a C++ host such as the plug-in can call;
+// bench.py uses one process per GPU instead).  Workers are spread round-robin over the devices and pull frames from one
+// shared counter, so a faster or less loaded GPU simply takes more frames; nothing is exchanged between devices.
+j2kcuda_sequence* j2kcuda_sequence_create_multi(const j2kcuda_params* p, const int* devices, int ndevices, int workers_per_device) { try {
+    int have = 0;
+    if (cudaGetDeviceCount(&have) != cudaSuccess || have == 0) { cudaGetLastError(); set_error(J2KCUDA_ERR_NO_DEVICE, "no CUDA device: libj2kcuda has no CPU path"); return nullptr; }
+    if (!devices || ndevices < 1 || ndevices > 64) { set_error(J2KCUDA_ERR_PARAM, "bad device list"); return nullptr; }
+    for (int i = 0; i < ndevices; ++i)
+        if (devices[i] < 0 || devices[i] >= have) { set_error(J2KCUDA_ERR_PARAM, "device ordinal out of range"); return nullptr; }
+    if (workers_per_device < 1) workers_per_device = 4;
+    if (workers_per_device > 16) workers_per_device = 16;
+    j2kcuda_sequence* s = new j2kcuda_sequence();
+    s->nworkers = ndevices * workers_per_device;
+    s->device = devices[0];
+    if (p) { s->have_params = true; s->params = *p; }
+    for (int w = 0; w < s->nworkers; ++w) s->devs.push_back(devices[w % ndevices]);
+    return s;
+} catch (...) { set_error(J2KCUDA_ERR_NOMEM, "j2kcuda_sequence_create_multi: out of memory or internal error"); return nullptr; } }
 
 void j2kcuda_sequence_destroy(j2kcuda_sequence* s) {
     if (!s) return;
@@ -99,7 +120,9 @@ int j2kcuda_sequence_encode(j2kcuda_sequence* s, const j2kcuda_plane* const* fra
     if (nframes <= 0) return J2KCUDA_OK;
     const int nw = s->nworkers < nframes ? s->nworkers : nframes;
     while ((int)s->enc.size() < nw) {            // contexts are created once and reused by later calls
-        j2kcuda_encoder* e = j2kcuda_encoder_create(&s->params);
+        j2kcuda_params pw = s->params;
+        pw.device = s->devs[s->enc.size()];
+        j2kcuda_encoder* e = j2kcuda_encoder_create(&pw);
         if (!e) return J2KCUDA_ERR_PARAM;        // message already set
         encoder_set_throughput_mode(e, s->nworkers > 2);
         s->enc.push_back(e);
@@ -132,7 +155,7 @@ int j2kcuda_sequence_decode(j2kcuda_sequence* s, const uint8_t* const* streams, 
     if (nframes <= 0) return J2KCUDA_OK;
     const int nw = s->nworkers < nframes ? s->nworkers : nframes;
     while ((int)s->dec.size() < nw) {
-        j2kcuda_decoder* d = j2kcuda_decoder_create(s->device);
+        j2kcuda_decoder* d = j2kcuda_decoder_create(s->devs[s->dec.size()]);
         if (!d) return J2KCUDA_ERR_NO_DEVICE;
         s->dec.push_back(d);
     }

@@ -83,14 +83,11 @@ int j2kcuda_t2_assemble(const j2kcuda_params* p, const j2kcuda_block_result* blo
         }
     }
     if (k != nblocks) return set_error(J2KCUDA_ERR_PARAM, "block count mismatch");
-    static thread_local std::vector<uint8_t> cs;     // keeps its pages between frames
-    cs.clear();
+    ByteBuf cs;
     std::string err;
     if (!host.assemble(tiles, cs, err)) return set_error(J2KCUDA_ERR_PARAM, err);
-    *out = (uint8_t*)out_alloc(cs.size());
-    if (!*out) return set_error(J2KCUDA_ERR_NOMEM, "malloc");
-    memcpy(*out, cs.data(), cs.size());
     *out_len = cs.size();
+    *out = cs.release();
     return J2KCUDA_OK;
 }); }
 
@@ -99,14 +96,11 @@ int j2kcuda_join_tile_streams(const j2kcuda_params* p, const uint8_t* const* fra
     if (!p || !frags || !lens || !out || !out_len || nfrags < 0) return set_error(J2KCUDA_ERR_PARAM, "null argument");
     CodingParams cp;
     setup_coding_params(*p, cp);
-    static thread_local std::vector<uint8_t> cs;     // keeps its pages between frames
-    cs.clear();
+    ByteBuf cs;
     std::string err;
     if (!join_tile_streams(cp, frags, lens, nfrags, cs, err)) return set_error(J2KCUDA_ERR_PARAM, err);
-    *out = (uint8_t*)out_alloc(cs.size());
-    if (!*out) return set_error(J2KCUDA_ERR_NOMEM, "malloc");
-    memcpy(*out, cs.data(), cs.size());
     *out_len = cs.size();
+    *out = cs.release();
     return J2KCUDA_OK;
 }); }
 

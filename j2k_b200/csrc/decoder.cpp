@@ -141,7 +141,7 @@ static int prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned 
     d->h_blocks.clear();
     size_t seg = 0;
     for (auto& t : d->host.tiles)
-        for (size_t k = 0; k < t.geo.cblks.size(); ++k)
+        for (size_t k = 0; k < t.geo.cblks.size(); ++k)                   // (tiles outside this context's range have no geometry)
             if (t.geo.cblks[k].res <= maxres) seg += (((size_t)t.blocks[k].len + 2) + 7) & ~(size_t)7;
     if (int rc = grow_host(d->h_seg, d->h_seg_cap, seg + 64)) return rc;
     seg = 0;
@@ -149,6 +149,7 @@ static int prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned 
     uint64_t nblk = 0;
     for (auto& t : d->host.tiles) {
         const TileGeo& g = t.geo;
+        if (g.comps.empty()) continue;
         for (int c = 0; c < d->ncomp; ++c) {
             const CompGeo& cg = g.comps[c];
             const size_t origin = (size_t)(cg.r.y0 - (int)cp.y0) * d->pitch + (cg.r.x0 - (int)cp.x0);
@@ -251,6 +252,7 @@ static int run(j2kcuda_decoder* d) {
     if (int rc = grow_dev(d->d_out, d->d_out_cap, out_bytes)) return rc;
     const int ix0 = (int)ceildivpow2(cp.x0, d->reduce), iy0 = (int)ceildivpow2(cp.y0, d->reduce);
     for (auto& t : d->host.tiles) {
+        if (t.geo.comps.empty()) continue;
         const CompGeo& cg = t.geo.comps[0];
         const int rx0 = (int)ceildivpow2((uint32_t)cg.r.x0, d->reduce), ry0 = (int)ceildivpow2((uint32_t)cg.r.y0, d->reduce);
         const int rx1 = (int)ceildivpow2((uint32_t)cg.r.x1, d->reduce), ry1 = (int)ceildivpow2((uint32_t)cg.r.y1, d->reduce);
@@ -310,7 +312,24 @@ static int download(j2kcuda_decoder* d, const j2kcuda_plane* planes, int nplanes
                 (int)p.width == d->outW && (int)p.height == d->outH && depth == cp.comps[c].prec && !p.sgnd == !cp.comps[c].sgnd;
     }
     CK(cudaEventRecord(d->ev[7], d->st));
-    if (tight) {
+    if (d->host.tile_count) {
+        // this context decoded a range of the frame's tiles (the others are on other GPUs): their rectangles go straight
+        // into the caller's image
+        if (!tight) return set_error(J2KCUDA_ERR_UNSUPPORTED, "tile-range decode needs a destination in the codestream's own layout");
+        const size_t row = (size_t)d->outW * d->ncomp * S;
+        const int ix0 = (int)ceildivpow2(cp.x0, d->reduce), iy0 = (int)ceildivpow2(cp.y0, d->reduce);
+        for (auto& t : d->host.tiles) {
+            if (t.geo.comps.empty()) continue;
+            const Rect& r = t.geo.comps[0].r;
+            const int rx0 = (int)ceildivpow2((uint32_t)r.x0, d->reduce) - ix0, ry0 = (int)ceildivpow2((uint32_t)r.y0, d->reduce) - iy0;
+            const int rx1 = (int)ceildivpow2((uint32_t)r.x1, d->reduce) - ix0, ry1 = (int)ceildivpow2((uint32_t)r.y1, d->reduce) - iy0;
+            if (rx1 <= rx0 || ry1 <= ry0) continue;
+            const size_t off = (size_t)ry0 * row + (size_t)rx0 * d->ncomp * S;
+            CK(cudaMemcpy2DAsync((uint8_t*)planes[0].buf + off, row, d->d_out + off, row, (size_t)(rx1 - rx0) * d->ncomp * S, (size_t)(ry1 - ry0),
+                                 cudaMemcpyDeviceToHost, d->st));
+        }
+        CK(stream_wait(d->st, d->ev_wait));
+    } else if (tight) {
         cudaPointerAttributes attr;
         bool pinned = cudaPointerGetAttributes(&attr, planes[0].buf) == cudaSuccess && attr.type == cudaMemoryTypeHost;
         cudaGetLastError();
@@ -418,6 +437,10 @@ void decoder_pool_clear() {
     { std::lock_guard<std::mutex> g(g_pool_mu); all.swap(g_pool); }
     for (auto* d : all) free_decoder(d);
 }
+}  // namespace j2k
+
+namespace j2k {
+void decoder_set_tile_range(::j2kcuda_decoder* d, uint32_t first, uint32_t count) { if (d) { d->host.tile_first = first; d->host.tile_count = count; } }
 }  // namespace j2k
 
 extern "C" {

@@ -480,7 +480,17 @@ int j2kcuda_encoder_finish(j2kcuda_encoder* e, uint8_t** out, size_t* out_len) {
     if (!e->ran) return set_error(J2KCUDA_ERR_PARAM, "encoder_run has not completed");
     auto t0 = std::chrono::steady_clock::now();
     const CodingParams& cp = e->cp;
-    for (size_t t = 0; t < e->tiles.size(); ++t) if (cp.tile_in_range((int)t)) init_enc_tile(cp, (int)t, e->tiles[t]);
+    for (size_t t = 0; t < e->tiles.size(); ++t) {
+        if (!cp.tile_in_range((int)t)) continue;
+        EncTile& tile = e->tiles[t];
+        if (tile.geo.cblks.empty()) { init_enc_tile(cp, (int)t, tile); continue; }
+        // the geometry and the tag trees of a context never change: only the per-frame block state is reset
+        for (auto& b : tile.blocks) {
+            b.numpasses = 0; b.numlenbits = 0; b.included_other = 0;
+            for (auto& l : b.layers) l = EncLayer();
+        }
+        tile.distotile = 0; tile.packno = 0;
+    }
     for (int i = 0; i < e->nblocks; ++i) {
         const T1Result& r = e->h_results[i];
         EncTile& tile = e->tiles[e->blk_tile[i]];
@@ -510,14 +520,11 @@ int j2kcuda_encoder_finish(j2kcuda_encoder* e, uint8_t** out, size_t* out_len) {
     EncoderHost host;
     host.cp = cp;
     host.ntiles = (int)e->tiles.size();
-    static thread_local std::vector<uint8_t> cs;     // keeps its pages between frames
-    cs.clear();
+    ByteBuf cs;                                      // built in place in the buffer the caller receives (recycled by j2kcuda_free)
     std::string err;
     if (!host.assemble(e->tiles, cs, err)) return set_error(J2KCUDA_ERR_PARAM, err);
-    *out = (uint8_t*)out_alloc(cs.size());
-    if (!*out) return set_error(J2KCUDA_ERR_NOMEM, "malloc");
-    memcpy(*out, cs.data(), cs.size());
     *out_len = cs.size();
+    *out = cs.release();
     e->ms[6] = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
     return J2KCUDA_OK;
 }); }

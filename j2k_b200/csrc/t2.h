@@ -4,6 +4,7 @@
 // Reference behaviour: ext/grok/src/lib/openjp2/{bio,tgt,pi,t2,tcd,j2k}.cpp (cited per function).
 #pragma once
 #include "geometry.h"
+#include "common.h"
 #include "../../include/j2kcuda.h"
 #include <cstdint>
 #include <cstring>
@@ -14,7 +15,7 @@ namespace j2k {
 
 // bio.cpp:99-235.  A byte that follows 0xFF carries 7 bits.
 struct BitWriter {
-    std::vector<uint8_t>* out = nullptr;   // null: count only (simulate)
+    ByteBuf* out = nullptr;                // null: count only (simulate)
     size_t n = 0;
     uint32_t buf = 0;
     int ct = 8;
@@ -92,14 +93,14 @@ struct EncoderHost {
     CodingParams cp;
     int ntiles = 0;
     // codestream assembly: tile results -> bytes
-    bool assemble(std::vector<EncTile>& tiles, std::vector<uint8_t>& out, std::string& err);
+    bool assemble(std::vector<EncTile>& tiles, ByteBuf& out, std::string& err);
 };
 
 const char* check_params(const ::j2kcuda_params& p);                      // nullptr = acceptable (j2k.cpp:6640-6680)
 void setup_coding_params(const ::j2kcuda_params& p, CodingParams& cp);   // j2k.cpp:5842-6216
 void init_enc_tile(const CodingParams& cp, int tileno, EncTile& t);
 bool join_tile_streams(const CodingParams& cp, const uint8_t* const* frags, const size_t* lens, int nfrags,
-                       std::vector<uint8_t>& out, std::string& err);
+                       ByteBuf& out, std::string& err);
 
 // ---- decoder side ---------------------------------------------------------------------------
 struct DecBlock {
@@ -120,6 +121,11 @@ struct DecTile {
 struct DecoderHost {
     CodingParams cp;
     std::vector<DecTile> tiles;
+    uint32_t tile_first = 0, tile_count = 0;      // read packets of these tiles only (0 = all): tiles of one frame over several GPUs
+    bool tile_in_range(int t) const { return tile_count == 0 || ((uint32_t)t >= tile_first && (uint32_t)t < tile_first + tile_count); }
+    // geometry of the previous codestream parsed by this object: frames of a sequence share it, so the tile / precinct /
+    // code-block tables and the tag trees are built once and only reset per frame
+    CodingParams prev_cp; bool have_prev = false; uint32_t prev_first = 0, prev_count = 0;
     bool parse_main_header(const uint8_t* d, size_t n, size_t& pos, std::string& err);
     bool parse(const uint8_t* d, size_t n, std::string& err);   // headers + packets for all tiles
 };

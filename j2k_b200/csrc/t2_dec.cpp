@@ -292,12 +292,28 @@ static bool read_packet(const CodingParams& cp, DecTile& t, const PacketId& pk, 
     return true;
 }
 
+static bool same_geometry(const CodingParams& a, const CodingParams& b) {
+    return a.x0 == b.x0 && a.y0 == b.y0 && a.x1 == b.x1 && a.y1 == b.y1 && a.tx0 == b.tx0 && a.ty0 == b.ty0 && a.tdx == b.tdx &&
+           a.tdy == b.tdy && a.ncomp == b.ncomp && a.csty == b.csty && a.numlayers == b.numlayers &&
+           memcmp(a.comps, b.comps, sizeof(a.comps)) == 0;
+}
+
 bool DecoderHost::parse(const uint8_t* d, size_t n, std::string& err) {
     size_t pos = 0;
-    if (!parse_main_header(d, n, pos, err)) return false;
-    if (!geometry_within_limits(cp, err)) return false;
+    have_prev = have_prev && !tiles.empty();
+    if (!parse_main_header(d, n, pos, err)) { have_prev = false; return false; }
+    if (!geometry_within_limits(cp, err)) { have_prev = false; return false; }
     const int nt = (int)(cp.tw * cp.th);
-    tiles.assign(nt, DecTile());
+    const bool reuse = have_prev && (int)tiles.size() == nt && prev_first == tile_first && prev_count == tile_count && same_geometry(prev_cp, cp);
+    have_prev = false;                               // set again only when this parse succeeds
+    if (!reuse) tiles.assign(nt, DecTile());
+    else
+        for (auto& t : tiles) {
+            t.parts.clear();
+            for (auto& b : t.blocks) { b.numbps = 0; b.npasses = 0; b.numlenbits = 3; b.included = false; b.chunks.clear(); b.len = 0; }
+            for (auto& tr : t.incl) tr.reset();
+            for (auto& tr : t.imsb) tr.reset();
+        }
     std::vector<std::vector<PocEntry>> tile_pocs(nt);
     // ---- tile-parts: j2k.cpp:7371-7640 ----
     for (;;) {
@@ -343,7 +359,8 @@ bool DecoderHost::parse(const uint8_t* d, size_t n, std::string& err) {
     for (int c = 0; c < cp.ncomp; ++c) maxres = std::max(maxres, cp.comps[c].numres);
     for (int tno = 0; tno < nt; ++tno) {
         DecTile& t = tiles[tno];
-        init_dec_tile(cp, tno, t);
+        if (!tile_in_range(tno)) { t.parts.clear(); continue; }     // another GPU's tile: no geometry, no packets
+        if (!reuse) init_dec_tile(cp, tno, t);
         if (t.parts.empty()) continue;
         std::vector<PocEntry> pocs = tile_pocs[tno].empty() ? cp.pocs : tile_pocs[tno];
         if (pocs.empty()) pocs.push_back(PocEntry{0, 0, cp.numlayers, maxres, cp.ncomp, cp.prog});
@@ -359,6 +376,7 @@ bool DecoderHost::parse(const uint8_t* d, size_t n, std::string& err) {
             if (!read_packet(cp, t, id, d, p, pend, err)) return false;
         }
     }
+    prev_cp = cp; prev_first = tile_first; prev_count = tile_count; have_prev = true;
     return true;
 }
 

@@ -173,7 +173,7 @@ static inline int tree_index(const CodingParams& cp, const EncTile& t, int c, in
 
 // ---- layer formation: tcd.cpp:321-417 ----------------------------------------------------------
 static void makelayer(const CodingParams& cp, EncTile& t, int layno, double thresh, bool final,
-                      bool include_all) {
+                      bool include_all, bool lossless = false) {
     for (auto& cblk : t.blocks) {
         EncLayer& layer = cblk.layers[layno];
         if (layno == 0) cblk.included_other = 0;
@@ -184,6 +184,7 @@ static void makelayer(const CodingParams& cp, EncTile& t, int layno, double thre
             else { dr = (uint32_t)(cblk.rates[passno] - cblk.rates[n - 1]); dd = cblk.dist[passno] - cblk.dist[n - 1]; }
             if (include_all) { n = passno + 1; continue; }     // OpenJPEG 2.5.x lossless layer
             if (!dr) { if (dd != 0) n = passno + 1; continue; }
+            if (lossless) { n = passno + 1; continue; }         // thresh = the tile's smallest slope: every slope passes, no division
             double slope = dd / dr;
             if (thresh - slope < DBL_EPSILON) n = passno + 1;
         }
@@ -216,7 +217,7 @@ static void putnumpasses(BitWriter& bio, uint32_t n) {
 // Writes one packet (out != null) or only counts its bytes (simulate: t2.cpp:832-1000; the
 // simulation walks the same header logic on the same mutable block state).
 static uint64_t encode_packet(const CodingParams& cp, EncTile& t, const PacketId& pk,
-                              std::vector<uint8_t>* out) {
+                              ByteBuf* out) {
     const int compno = pk.compno, resno = pk.resno, precno = pk.precno, layno = pk.layno;
     const ResGeo& res = t.geo.comps[compno].res[resno];
     uint64_t nbytes = 0;
@@ -465,6 +466,11 @@ static bool simulate_cached(const CodingParams& cp, EncTile& t, uint64_t maxlen,
 static void pcrd_bisect(const CodingParams& cp, EncTile& t, const std::vector<TilePart>& parts,
                         const double* rates, uint64_t len) {
     double min_slope = DBL_MAX, max_slope = 0;
+    bool any_rate = false;
+    for (int layno = 0; layno < cp.numlayers; ++layno) any_rate |= rates[layno] > 0.0;
+    // lossless layers only (the plug-in's case): the threshold would be the smallest slope of the tile, which every pass
+    // meets -- the slopes need not be computed at all (tcd.cpp:180-239, 309, 356-382)
+    if (any_rate)
     for (auto& cblk : t.blocks)
         for (int passno = 0; passno < cblk.totalpasses; ++passno) {
             int32_t dr; double dd;
@@ -499,12 +505,12 @@ static void pcrd_bisect(const CodingParams& cp, EncTile& t, const std::vector<Ti
             goodthresh = min_slope;
             all = cp.compat == J2KCUDA_COMPAT_OPENJPEG_2_5 || cp.compat == J2KCUDA_COMPAT_OPENJPEG_2_5_3;
         }
-        makelayer(cp, t, layno, goodthresh, true, all);
+        makelayer(cp, t, layno, goodthresh, true, all, !any_rate);
     }
 }
 
 // ---- markers: j2k.cpp:1871-4340 ---------------------------------------------------------------
-static void put(std::vector<uint8_t>& o, uint64_t v, int nbytes) {
+template <class B> static void put(B& o, uint64_t v, int nbytes) {
     for (int i = nbytes - 1; i >= 0; --i) o.push_back((uint8_t)(v >> (8 * i)));
 }
 static void write_spcod(std::vector<uint8_t>& o, const CompParams& t) {      // :8289-8370
@@ -536,7 +542,7 @@ static bool same_quant(const CompParams& a, const CompParams& b) {           // 
     return true;
 }
 
-static void write_main_header(const CodingParams& cp, int total_tile_parts, std::vector<uint8_t>& o,
+static void write_main_header(const CodingParams& cp, int total_tile_parts, ByteBuf& o,
                               size_t& tlm_pos) {
     put(o, 0xff4f, 2);                                                        // SOC
     put(o, 0xff51, 2); put(o, 38 + 3 * cp.ncomp, 2); put(o, cp.rsiz, 2);       // SIZ :1938-2030
@@ -576,7 +582,7 @@ static void write_main_header(const CodingParams& cp, int total_tile_parts, std:
     if (cinema) {                                                             // TLM :3772-3824
         put(o, 0xff55, 2); put(o, 4 + 5 * total_tile_parts, 2); put(o, 0, 1); put(o, 0x50, 1);
         tlm_pos = o.size();
-        o.resize(o.size() + 5 * (size_t)total_tile_parts, 0);
+        for (int k = 0; k < 5 * total_tile_parts; ++k) o.push_back(0);
         if (cp.rsiz == J2KCUDA_PROFILE_CINEMA_4K && !cp.pocs.empty()) {       // POC :2947-3069
             put(o, 0xff5f, 2); put(o, 2 + 7 * cp.pocs.size(), 2);
             for (auto& pe : cp.pocs) {
@@ -591,7 +597,7 @@ static void write_main_header(const CodingParams& cp, int total_tile_parts, std:
     }
 }
 
-bool EncoderHost::assemble(std::vector<EncTile>& tiles, std::vector<uint8_t>& out, std::string& err) {
+bool EncoderHost::assemble(std::vector<EncTile>& tiles, ByteBuf& out, std::string& err) {
     const int nt = (int)(cp.tw * cp.th);
     auto tS = std::chrono::steady_clock::now();
     if ((int)tiles.size() != nt) { err = "tile count mismatch"; return false; }
@@ -694,7 +700,7 @@ bool EncoderHost::assemble(std::vector<EncTile>& tiles, std::vector<uint8_t>& ou
 // One frame from the tile-part fragments of several encoders (tile ranges): main header, the
 // fragments ordered by the tile index of their first SOT, EOC.
 bool join_tile_streams(const CodingParams& cp_in, const uint8_t* const* frags, const size_t* lens, int nfrags,
-                       std::vector<uint8_t>& out, std::string& err) {
+                       ByteBuf& out, std::string& err) {
     CodingParams cp = cp_in;
     cp.tile_first = cp.tile_count = 0;
     const int nt = (int)(cp.tw * cp.th);

@@ -141,3 +141,66 @@ def test_one_shot_calls_are_reentrant():
     for t in threads:
         t.join()
     assert not errors, errors
+
+
+# ---- several GPUs behind one call (here: the same device listed more than once, which exercises the same code paths) ----
+def _devices(n):
+    import torch
+    have = torch.cuda.device_count()
+    return [i % have for i in range(n)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ndev", [2, 3])
+def test_tiles_of_one_frame_over_several_devices(ndev):
+    """j2kcuda_tiles_*: contiguous tile runs per device, fragments joined on the host: byte-identical to a one-device encode;
+    decode routes tile-parts by SOT tile index and every device writes its own rectangles"""
+    import j2k
+    lib = L.lib()
+    img = make_frame(300, 420, 3, 16, "smooth", seed=21)
+    kw = dict(mct=1, tile_w=128, tile_h=128, numresolution=4)
+    whole = j2k.encode(img, 16, **kw)
+    p = L.default_params(width=420, height=300, ncomp=3, prec=16, **kw)
+    devs = (C.c_int * ndev)(*_devices(ndev))
+    lib.j2kcuda_tiles_create.restype = C.c_void_p
+    t = C.c_void_p(lib.j2kcuda_tiles_create(C.byref(p), devs, ndev))
+    assert t.value, L.last_error()
+    for _ in range(2):                                               # second frame reuses the contexts
+        out = C.POINTER(C.c_uint8)(); n = C.c_size_t(0)
+        assert lib.j2kcuda_tiles_encode(t, j2k.planes_of(img), 3, C.byref(out), C.byref(n)) == 0, L.last_error()
+        data = C.string_at(out, n.value); lib.j2kcuda_free(out)
+        assert data == whole
+        back = np.zeros_like(img)
+        assert lib.j2kcuda_tiles_decode(t, data, C.c_size_t(len(data)), 0, j2k.planes_of(back), 3) == 0, L.last_error()
+        assert np.array_equal(back, img)
+    half = np.zeros((150, 210, 3), np.uint16)
+    assert lib.j2kcuda_tiles_decode(t, whole, C.c_size_t(len(whole)), 1, j2k.planes_of(half), 3) == 0, L.last_error()
+    assert np.array_equal(half, j2k.decode(whole, reduce=1))
+    lib.j2kcuda_tiles_destroy(t)
+
+
+@pytest.mark.gpu
+def test_sequence_over_several_devices():
+    import j2k
+    lib = L.lib()
+    frames = [make_frame(96, 160, 3, 8, "smooth", seed=s) for s in range(7)]
+    p = L.default_params(width=160, height=96, ncomp=3, prec=8, mct=1)
+    devs = (C.c_int * 2)(*_devices(2))
+    lib.j2kcuda_sequence_create_multi.restype = C.c_void_p
+    s = C.c_void_p(lib.j2kcuda_sequence_create_multi(C.byref(p), devs, 2, 2))
+    assert s.value, L.last_error()
+    keep = [j2k.planes_of(f) for f in frames]
+    tab = (C.POINTER(L.Plane) * len(frames))(*[C.cast(k, C.POINTER(L.Plane)) for k in keep])
+    outs = (C.POINTER(C.c_uint8) * len(frames))(); lens = (C.c_size_t * len(frames))()
+    assert lib.j2kcuda_sequence_encode(s, tab, len(frames), 3, 0, outs, lens) == 0, L.last_error()
+    for i, f in enumerate(frames):
+        assert C.string_at(outs[i], lens[i]) == j2k.encode(f, 8, mct=1)
+    back = [np.zeros_like(f) for f in frames]
+    keep2 = [j2k.planes_of(b) for b in back]
+    tab2 = (C.POINTER(L.Plane) * len(frames))(*[C.cast(k, C.POINTER(L.Plane)) for k in keep2])
+    assert lib.j2kcuda_sequence_decode(s, C.cast(outs, C.POINTER(C.POINTER(C.c_uint8))), lens, len(frames), 0, tab2, 3, 0) == 0, L.last_error()
+    for b, f in zip(back, frames):
+        assert np.array_equal(b, f)
+    for i in range(len(frames)):
+        lib.j2kcuda_free(outs[i])
+    lib.j2kcuda_sequence_destroy(s)
