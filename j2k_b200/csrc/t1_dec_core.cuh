@@ -38,69 +38,104 @@ struct DRows {                // index = row + 1
 // any of its bytes is needed.  The segment must start 8-byte aligned, be followed by two 0xFF bytes
 // (which reproduces the reference's behaviour at and past the end of the data, mqc.cpp:336-365) and
 // by at least 24 more readable bytes.
-struct MqDec {
-    uint32_t a, c, ct;        // a is kept shifted left by 16 so that it lines up with the code bits of c
+// The byte window of the segment lives in shared memory (one per warp), not in registers: it is touched only when the
+// code register runs dry, about once per ten decisions, and that refill is ONE out-of-line routine instead of a copy at
+// each of the eight places a decision is decoded -- the decision loops stay small enough for the instruction cache and
+// the decoder state in registers shrinks to a, c, ct.
+struct MqIo {
     const u64* wp;            // next word to fetch
     u64 w0, w1;               // bytes [8k, 8k+8) and [8k+8, 8k+16) of the segment
     uint32_t off;             // position of the current byte inside w0
-    J2K_HD inline void advance() {
-        if (++off == 8) { off = 0; w0 = w1; w1 = *wp++; }
+    uint32_t pad;
+};
+J2K_HD inline void mq_io_bytein(MqIo* io, uint32_t& c, uint32_t& ct) {            // mqc.cpp:336-365
+    const u64 w0 = io->w0;
+    const uint32_t off = io->off;
+    const uint32_t cur = (uint32_t)(w0 >> (8 * off)) & 0xffu;
+    const uint32_t nxt = off < 7 ? (uint32_t)(w0 >> (8 * off + 8)) & 0xffu : (uint32_t)io->w1 & 0xffu;
+    bool adv = true;
+    if (cur == 0xffu) {
+        if (nxt > 0x8fu) { c += 0xff00u; ct = 8; adv = false; }
+        else { c += nxt << 9; ct = 7; }
+    } else { c += nxt << 8; ct = 8; }
+    if (adv) {
+        if (off == 7) { io->off = 0; io->w0 = io->w1; io->w1 = *io->wp; io->wp = io->wp + 1; }
+        else io->off = off + 1;
     }
-    J2K_HD inline void bytein() {
-        const uint32_t cur = (uint32_t)(w0 >> (8 * off)) & 0xffu;
-        const uint32_t nxt = off < 7 ? (uint32_t)(w0 >> (8 * off + 8)) & 0xffu : (uint32_t)w1 & 0xffu;
-        if (cur == 0xffu) {
-            if (nxt > 0x8fu) { c += 0xff00u; ct = 8; }
-            else { advance(); c += nxt << 9; ct = 7; }
-        } else { advance(); c += nxt << 8; ct = 8; }
-    }
-    J2K_HD void init(const uint8_t* p) {                  // mqc.cpp:560-575
-        wp = reinterpret_cast<const u64*>(p);
-        w0 = *wp++; w1 = *wp++;
-        off = 0;
-        c = ((uint32_t)w0 & 0xffu) << 16;
-        bytein();
+}
+// shift the code register by n > ct bits, fetching bytes as they are needed (mqc.cpp:367-378); returns c | ct << 32
+J2K_HD J2K_NOINLINE u64 mq_refill(MqIo* io, uint32_t c, uint32_t ct, uint32_t n) {
+    do {
+        c <<= ct; n -= ct;
+        mq_io_bytein(io, c, ct);
+    } while (n > ct);
+    c <<= n; ct -= n;
+    return (u64)c | ((u64)ct << 32);
+}
+
+struct MqDec {
+    uint32_t a, c, ct;        // a is kept shifted left by 16 so that it lines up with the code bits of c
+    MqIo* io;
+    J2K_HD void init(MqIo* io_, const uint8_t* p) {       // mqc.cpp:560-575
+        io = io_;
+        const u64* wp = reinterpret_cast<const u64*>(p);
+        io->w0 = wp[0]; io->w1 = wp[1]; io->wp = wp + 2; io->off = 0;
+        c = ((uint32_t)io->w0 & 0xffu) << 16;
+        mq_io_bytein(io, c, ct);
         c <<= 7; ct -= 7; a = 0x80000000u;
     }
     J2K_HD inline void renorm() {                         // a < 0x8000: shift until the top bit is set, refilling c
-        uint32_t n = (uint32_t)J2K_CLZ(a);                // (bytes are fetched only when a shift needs them, mqc.cpp:367-378)
+        const uint32_t n = (uint32_t)J2K_CLZ(a);
         a <<= n;
-        if (n > ct) {
-            do {
-                c <<= ct; n -= ct;
-                bytein();
-            } while (n > ct);
-        }
-        c <<= n; ct -= n;
+        if (n > ct) { const u64 r = mq_refill(io, c, ct, n); c = (uint32_t)r; ct = (uint32_t)(r >> 32); }
+        else { c <<= n; ct -= n; }
     }
     // st: per-context state WORD = the probability-table entry of the context's current state:
-    //   qe << 16 | next-if-LPS << 8 | next-if-MPS << 1 | mps   (next-* index the table, tab = mq_state_words).
+    //   qe << 16 | next-if-LPS << 9 | next-if-MPS << 2 | mps   (next-* are byte offsets into the table, tab = mq_state_words).
     // One shared-memory look-up per decision, a second only when the state moves.
     J2K_HD inline uint32_t decode(uint32_t* st, const uint32_t* tab, uint32_t ctx) {   // mqc.cpp:577-595
         const uint32_t e = st[ctx], qe = e & 0xffff0000u;
-        uint32_t d = e & 1u;
+        const uint32_t d = e & 1u;
         a -= qe;
-        if (c < qe) {
-            if (a < qe) st[ctx] = tab[(e >> 1) & 0x7fu];
-            else { d ^= 1u; st[ctx] = tab[(e >> 8) & 0x7fu]; }
-            a = qe;
-            renorm();
-        } else {
+        const bool lower = c < qe;                       // the code lies in the LPS sub-interval
+        if (!lower) {
             c -= qe;
-            if ((int32_t)a >= 0) {
-                if (a < qe) { d ^= 1u; st[ctx] = tab[(e >> 8) & 0x7fu]; }
-                else st[ctx] = tab[(e >> 1) & 0x7fu];
-                renorm();
-            }
+            if ((int32_t)a < 0) return d;                // MPS, no renormalisation: the common case
         }
-        return d;
+        // one copy of the state move and the renormalisation for the three remaining cases: the symbol is the LPS when
+        // exactly one of "code in the lower sub-interval" and "conditional exchange (a < qe)" holds
+        const uint32_t flip = (uint32_t)lower ^ (uint32_t)(a < qe);
+        st[ctx] = *reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(tab) + ((flip ? (e >> 7) : e) & 0x1fcu));
+        if (lower) a = qe;
+        renorm();
+        return d ^ flip;
+    }
+    // The same step with the state word of the context used last held in a register (lc, le): runs of one context --
+    // the refinement pass of a dense block codes almost everything with MAG + 2 -- skip the shared-memory store and
+    // the load that would have to wait for it.  st[lc] is stale until flush_cached().
+    J2K_HD inline uint32_t decode_cached(uint32_t* st, const uint32_t* tab, uint32_t ctx, uint32_t& lc, uint32_t& le) {
+        if (ctx != lc) { st[lc] = le; le = st[ctx]; lc = ctx; }
+        const uint32_t e = le, qe = e & 0xffff0000u;
+        const uint32_t d = e & 1u;
+        a -= qe;
+        const bool lower = c < qe;
+        if (!lower) {
+            c -= qe;
+            if ((int32_t)a < 0) return d;
+        }
+        const uint32_t flip = (uint32_t)lower ^ (uint32_t)(a < qe);
+        le = *reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(tab) + ((flip ? (e >> 7) : e) & 0x1fcu));
+        if (lower) a = qe;
+        renorm();
+        return d ^ flip;
     }
 };
 
 // state word table from T1Tables::mq (entry s = state index * 2 + mps: qe | next-if-MPS << 16 | next-if-LPS << 24)
 J2K_HD inline uint32_t mq_state_word(const uint32_t* mq, int s) {
     const uint32_t m = mq[s];
-    return ((m & 0xffffu) << 16) | ((m >> 24) << 8) | (((m >> 16) & 0x7fu) << 1) | (uint32_t)(s & 1);
+    // qe << 16 | next-if-LPS << 9 | next-if-MPS << 2 | mps: the next-state fields are BYTE offsets into the table (index * 4)
+    return ((m & 0xffffu) << 16) | ((m >> 24) << 9) | (((m >> 16) & 0x7fu) << 2) | (uint32_t)(s & 1);
 }
 
 J2K_HD inline uint32_t w3(u64 m, int x) {          // bits x-1, x, x+1 of a row
@@ -192,7 +227,7 @@ J2K_HD inline uint32_t spread4(uint32_t n) {
 // Decode one code-block.  Called by all `nlanes` lanes of a warp with identical arguments except `lane`;
 // the decision loop runs redundantly on warp-uniform data, the lane index only partitions the
 // column-parallel parts (stripe set-up and write-back, fold, final pass).  R and st must be zero / reset on entry.
-J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uint32_t* st, const uint8_t* zc_all, const uint8_t* sc,
+J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, MqIo* io, uint32_t* st, const uint8_t* zc_all, const uint8_t* sc,
                                 const uint32_t* mqtab, const uint8_t* seg_arena, int raw_output, int lane, int nlanes) {
     const int w = blk.w, h = blk.h;
     int32_t* out = blk.coeff;
@@ -201,7 +236,7 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
     const u64 colmask = w == 64 ? ~0ull : ((1ull << w) - 1);
 
     MqDec mq;
-    mq.init(seg_arena + blk.data_off);
+    mq.init(io, seg_arena + blk.data_off);
 
     int bp = blk.numbps - 1;              // 0-based bit-plane being decoded
     int passtype = 2;
@@ -326,6 +361,7 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
             } else if (passtype == 1) {
                 // magnitude refinement: significant and not coded in this plane's first pass; decisions come out in
                 // list order and are put back on their rows by the lanes afterwards
+                uint32_t mr_lc = CTX_MAG + 2, mr_le = st[CTX_MAG + 2];
 #pragma unroll 1
                 for (int hh = 0; hh < 2; ++hh) {
                 uint32_t c32 = (uint32_t)(cols >> (32 * hh));
@@ -334,12 +370,13 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, uin
                     c32 &= c32 - 1;
                     uint32_t list = cb.aux[x] >> 8, res = 0, k = 0;
                     do {
-                        res |= mq.decode(st, mqtab, CTX_MAG - 1 + (list & 3u)) << k;
+                        res |= mq.decode_cached(st, mqtab, CTX_MAG - 1 + (list & 3u), mr_lc, mr_le) << k;
                         ++k; list >>= 2;
                     } while (list);
                     if (res) { cb.out[x] = res; any = true; }
                 }
                 }
+                st[mr_lc] = mr_le;
             } else {
                 // cleanup: everything not yet significant and not visited
 #pragma unroll 1

@@ -29,7 +29,8 @@ extern "C" int t1dec_host_block(const uint8_t* data, int len, int w, int h, int 
     static ColBuf cb;
     uint8_t sc2[256];
     for (int i = 0; i < 256; ++i) sc2[i] = sc_entry(sc, i);
-    decode_block(b, R, cb, st, zc9, sc2, tab, seg.data(), 1, 0, 1);
+    static MqIo io;
+    decode_block(b, R, cb, &io, st, zc9, sc2, tab, seg.data(), 1, 0, 1);
     return 0;
 }
 
