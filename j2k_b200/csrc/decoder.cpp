@@ -41,6 +41,10 @@ struct j2kcuda_decoder {
     int32_t* planeB[4] = {nullptr, nullptr, nullptr, nullptr};
     // per-frame tables
     std::vector<T1DecBlock> h_blocks;
+    std::vector<T1DecSeg> h_segs;                                             // codeword segments of blocks that have several
+    T1DecSeg* d_segs = nullptr; size_t d_segs_cap = 0;
+    bool generic = false;                                                     // some block needs the generic Tier-1 variant
+    bool subsampled = false;                                                  // some component has dx or dy != 1
     T1DecBlock* d_blocks = nullptr; size_t d_blocks_cap = 0;
     uint8_t* h_seg = nullptr; size_t h_seg_cap = 0;                           // pinned
     uint8_t* d_seg = nullptr; size_t d_seg_cap = 0;
@@ -62,7 +66,7 @@ static void free_decoder(j2kcuda_decoder* d) {
     if (!d) return;
     cudaSetDevice(d->device);
     for (int c = 0; c < 4; ++c) { cudaFree(d->planeA[c]); cudaFree(d->planeB[c]); }
-    cudaFree(d->d_blocks); cudaFree(d->d_seg); cudaFree(d->d_jobs); cudaFree(d->d_out); cudaFree(d->d_stage);
+    cudaFree(d->d_blocks); cudaFree(d->d_segs); cudaFree(d->d_seg); cudaFree(d->d_jobs); cudaFree(d->d_out); cudaFree(d->d_stage);
     cudaFreeHost(d->h_seg); cudaFreeHost(d->h_out);
     for (auto& e : d->ev) if (e) cudaEventDestroy(e);
     if (d->ev_wait) cudaEventDestroy(d->ev_wait);
@@ -108,13 +112,23 @@ static int prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned 
     std::string err;
     if (!d->host.parse(cs, len, err)) return set_error(J2KCUDA_ERR_STREAM, err);
     const CodingParams& cp = d->host.cp;
+    bool subsampled = false;
     for (int c = 0; c < cp.ncomp; ++c) {
-        if (cp.comps[c].dx != 1 || cp.comps[c].dy != 1) return set_error(J2KCUDA_ERR_UNSUPPORTED, "sub-sampled components are not supported");
+        if (cp.comps[c].dx != 1 || cp.comps[c].dy != 1) subsampled = true;
         if (cp.comps[c].numres != cp.comps[0].numres || cp.comps[c].qmfbid != cp.comps[0].qmfbid)
             return set_error(J2KCUDA_ERR_UNSUPPORTED, "components with different decompositions are not supported");
         if (cp.comps[c].cblkw > 6 || cp.comps[c].cblkh > 6) return set_error(J2KCUDA_ERR_UNSUPPORTED, "code-blocks larger than 64x64 samples");
         if (cp.comps[c].prec > 16) return set_error(J2KCUDA_ERR_UNSUPPORTED, "more than 16 bits per sample");
     }
+    if (subsampled) {
+        // components at a lower resolution than the reference grid (chroma sub-sampling): decoded at their own size, replicated
+        // into the output as Codec::CopyBuffer does it above the reference codec (src/common/j2k_codec.cpp:262-279)
+        if (cp.comps[0].dx != 1 || cp.comps[0].dy != 1) return set_error(J2KCUDA_ERR_UNSUPPORTED, "sub-sampled first component");
+        if (cp.mct) return set_error(J2KCUDA_ERR_UNSUPPORTED, "multi-component transform over sub-sampled components");
+        if (reduce > 0 && cp.tw * cp.th > 1) return set_error(J2KCUDA_ERR_UNSUPPORTED, "reduced decode of a tiled image with sub-sampled components");
+        if (d->host.tile_count) return set_error(J2KCUDA_ERR_UNSUPPORTED, "tile-range decode with sub-sampled components");
+    }
+    d->subsampled = subsampled;
     d->numres = cp.comps[0].numres;
     if ((int)reduce >= d->numres) return set_error(J2KCUDA_ERR_PARAM, "reduce exceeds the number of resolutions");   // j2k.cpp read_SPCod check
     d->reduce = reduce;
@@ -138,11 +152,12 @@ static int prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned 
     // ---- block table + segment arena ----
     const int levels = d->numres - 1;
     const int maxres = d->numres - 1 - (int)reduce;
-    d->h_blocks.clear();
+    d->h_blocks.clear(); d->h_segs.clear();
+    bool generic = false;
     size_t seg = 0;
     for (auto& t : d->host.tiles)
         for (size_t k = 0; k < t.geo.cblks.size(); ++k)                   // (tiles outside this context's range have no geometry)
-            if (t.geo.cblks[k].res <= maxres) seg += (((size_t)t.blocks[k].len + 2) + 7) & ~(size_t)7;
+            if (t.geo.cblks[k].res <= maxres) seg += ((((size_t)t.blocks[k].len + 2) + 7) & ~(size_t)7) + 16 * t.blocks[k].segs.size();
     if (int rc = grow_host(d->h_seg, d->h_seg_cap, seg + 64)) return rc;
     seg = 0;
     d->level_jobs.assign(levels, {});
@@ -152,7 +167,7 @@ static int prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned 
         if (g.comps.empty()) continue;
         for (int c = 0; c < d->ncomp; ++c) {
             const CompGeo& cg = g.comps[c];
-            const size_t origin = (size_t)(cg.r.y0 - (int)cp.y0) * d->pitch + (cg.r.x0 - (int)cp.x0);
+            const size_t origin = (size_t)(cg.r.y0 - (int)ceildiv(cp.y0, cp.comps[c].dy)) * d->pitch + (cg.r.x0 - (int)ceildiv(cp.x0, cp.comps[c].dx));
             for (int l = levels; l > (int)reduce; --l) {
                 const ResGeo& outr = cg.res[d->numres - l];          // region this inverse level produces
                 if (outr.r.w() <= 0 || outr.r.h() <= 0) continue;
@@ -175,20 +190,44 @@ static int prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned 
             memset(&b, 0, sizeof(b));
             const int level = cb.res == 0 ? levels : d->numres - cb.res;
             int32_t* plane = (level & 1) ? d->planeB[cb.comp] : d->planeA[cb.comp];
-            b.coeff = plane + (size_t)(cg.r.y0 - (int)cp.y0 + cb.py) * d->pitch + (cg.r.x0 - (int)cp.x0 + cb.px);
+            b.coeff = plane + (size_t)(cg.r.y0 - (int)ceildiv(cp.y0, cp.comps[cb.comp].dy) + cb.py) * d->pitch + (cg.r.x0 - (int)ceildiv(cp.x0, cp.comps[cb.comp].dx) + cb.px);
             b.pitch = d->pitch;
             b.w = (uint16_t)cb.r.w(); b.h = (uint16_t)cb.r.h();
             b.orient = (uint8_t)cb.orient; b.qmfbid = (uint8_t)cp.comps[cb.comp].qmfbid;
             int nbps = db.included ? db.numbps : 0;
-            if (nbps > 30) return set_error(J2KCUDA_ERR_STREAM, "code-block with more than 30 bit-planes");
+            const int roishift = cp.comps[cb.comp].roishift, sty = cp.comps[cb.comp].cblksty;
+            if (nbps + roishift > 30) return set_error(J2KCUDA_ERR_STREAM, "code-block with more than 30 bit-planes");
             b.numbps = (uint8_t)std::max(nbps, 0);
-            b.npasses = (uint8_t)std::min(db.npasses, 3 * nbps - 2 > 0 ? 3 * nbps - 2 : 0);
+            const int maxp = 3 * (nbps + roishift) - 2;
+            b.npasses = (uint8_t)std::min(db.npasses, maxp > 0 ? maxp : 0);
             b.stepsize = band.stepsize;
+            b.cblksty = (uint8_t)sty; b.roishift = (uint8_t)roishift;
+            b.nsegs = (uint16_t)std::max<size_t>(db.segs.size(), 1);
+            if (sty || roishift || db.segs.size() > 1) generic = true;
             b.data_off = (uint32_t)seg; b.data_len = (uint32_t)db.len;
-            uint8_t* p = d->h_seg + seg;
-            for (auto& ch : db.chunks) { memcpy(p, cs + ch.first, ch.second); p += ch.second; }
-            p[0] = 0xff; p[1] = 0xff;
-            seg += (((size_t)db.len + 2) + 7) & ~(size_t)7;
+            if (db.segs.size() <= 1) {
+                uint8_t* p = d->h_seg + seg;
+                for (auto& ch : db.chunks) { memcpy(p, cs + ch.first, ch.second); p += ch.second; }
+                p[0] = 0xff; p[1] = 0xff;
+                seg += (((size_t)db.len + 2) + 7) & ~(size_t)7;
+            } else {
+                // several codeword segments: each one 8-byte aligned and followed by 0xFF 0xFF, as the MQ reader wants them
+                static thread_local std::vector<uint8_t> flat;
+                flat.clear();
+                for (auto& ch : db.chunks) flat.insert(flat.end(), cs + ch.first, cs + ch.first + ch.second);
+                b.seg_index = (uint32_t)d->h_segs.size();
+                size_t in = 0;
+                int passes_left = b.npasses;
+                for (auto& sg : db.segs) {
+                    const size_t sl = std::min<size_t>((size_t)sg.len, flat.size() - in);
+                    const int np = std::min(sg.numpasses, passes_left);
+                    memcpy(d->h_seg + seg, flat.data() + in, sl);
+                    d->h_seg[seg + sl] = 0xff; d->h_seg[seg + sl + 1] = 0xff;
+                    d->h_segs.push_back(T1DecSeg{(uint32_t)seg, (uint32_t)sl, (uint32_t)np, 0});
+                    in += sl; passes_left -= np;
+                    seg += ((sl + 2) + 7) & ~(size_t)7;
+                }
+            }
             d->h_blocks.push_back(b);
             ++nblk;
         }
@@ -218,6 +257,9 @@ static int prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned 
     if (int rc = grow_dev(d->d_blocks, d->d_blocks_cap, d->h_blocks.size() * sizeof(T1DecBlock))) return rc;
     if (int rc = grow_dev(d->d_jobs, d->d_jobs_cap, all.size() * sizeof(DwtJob))) return rc;
     if (seg) CK(cudaMemcpyAsync(d->d_seg, d->h_seg, seg, cudaMemcpyHostToDevice, d->st));
+    d->generic = generic;
+    if (int rc = grow_dev(d->d_segs, d->d_segs_cap, (d->h_segs.size() + 1) * sizeof(T1DecSeg))) return rc;
+    if (!d->h_segs.empty()) CK(cudaMemcpyAsync(d->d_segs, d->h_segs.data(), d->h_segs.size() * sizeof(T1DecSeg), cudaMemcpyHostToDevice, d->st));
     if (!d->h_blocks.empty()) CK(cudaMemcpyAsync(d->d_blocks, d->h_blocks.data(), d->h_blocks.size() * sizeof(T1DecBlock), cudaMemcpyHostToDevice, d->st));
     if (!all.empty()) CK(cudaMemcpyAsync(d->d_jobs, all.data(), all.size() * sizeof(DwtJob), cudaMemcpyHostToDevice, d->st));
     CK(cudaEventRecord(d->ev[1], d->st));
@@ -235,7 +277,7 @@ static int run(j2kcuda_decoder* d) {
     cudaStream_t st = d->st;
     uint64_t launches = 0;
     CK(cudaEventRecord(d->ev[2], st));
-    launch_t1_decode(d->d_blocks, (int)d->h_blocks.size(), d->d_seg, 0, st); ++launches;
+    launch_t1_decode(d->d_blocks, (int)d->h_blocks.size(), d->d_seg, d->d_segs, d->generic ? 1 : 0, 0, st); ++launches;
     CK(cudaEventRecord(d->ev[3], st));
     const int levels = d->numres - 1;
     for (int l = levels; l > (int)d->reduce; --l) {
@@ -251,6 +293,21 @@ static int run(j2kcuda_decoder* d) {
     const size_t out_bytes = (size_t)d->outW * d->outH * d->ncomp * d->S;
     if (int rc = grow_dev(d->d_out, d->d_out_cap, out_bytes)) return rc;
     const int ix0 = (int)ceildivpow2(cp.x0, d->reduce), iy0 = (int)ceildivpow2(cp.y0, d->reduce);
+    if (d->subsampled) {
+        SubOut so;
+        memset(&so, 0, sizeof(so));
+        so.width = d->outW; so.height = d->outH; so.pitch = d->pitch; so.ncomp = d->ncomp; so.sample_bytes = d->S;
+        so.irreversible = d->irreversible; so.sgnd = cp.comps[0].sgnd;
+        for (int c = 0; c < d->ncomp; ++c) {
+            so.plane[c] = (d->reduce & 1) ? d->planeB[c] : d->planeA[c];
+            so.dx[c] = cp.comps[c].dx; so.dy[c] = cp.comps[c].dy;
+            so.cw[c] = (int)(ceildivpow2(ceildiv(cp.x1, cp.comps[c].dx), d->reduce) - ceildivpow2(ceildiv(cp.x0, cp.comps[c].dx), d->reduce));
+            so.ch[c] = (int)(ceildivpow2(ceildiv(cp.y1, cp.comps[c].dy), d->reduce) - ceildivpow2(ceildiv(cp.y0, cp.comps[c].dy), d->reduce));
+            so.prec[c] = cp.comps[c].prec; so.dc_shift[c] = cp.comps[c].sgnd ? 0 : 1 << (cp.comps[c].prec - 1);
+        }
+        launch_output_subsampled(so, d->d_out, st);
+        ++launches;
+    } else
     for (auto& t : d->host.tiles) {
         if (t.geo.comps.empty()) continue;
         const CompGeo& cg = t.geo.comps[0];
@@ -382,7 +439,14 @@ static int download(j2kcuda_decoder* d, const j2kcuda_plane* planes, int nplanes
             const j2kcuda_plane& p = planes[c];
             const int depth = p.depth ? p.depth : cp.comps[c].prec;
             const CopyConv cc = make_copy_conv(J2KCUDA_INT, cp.comps[c].prec, cp.comps[c].sgnd, p.sample_type, depth, p.sgnd);
-            launch_copy_channel(d->d_out, S, d->ncomp, c, cp.comps[0].sgnd, d->outW, (int)p.width, (int)p.height, d->d_stage + offs[c], cc, d->st);
+            // a plane of exactly the component's own (sub-sampled) size takes the component's samples, any other the replicated image
+            int sx = 1, sy = 1;
+            if (cp.comps[c].dx > 1 || cp.comps[c].dy > 1) {
+                const int cw = (int)(ceildivpow2(ceildiv(cp.x1, cp.comps[c].dx), d->reduce) - ceildivpow2(ceildiv(cp.x0, cp.comps[c].dx), d->reduce));
+                const int chh = (int)(ceildivpow2(ceildiv(cp.y1, cp.comps[c].dy), d->reduce) - ceildivpow2(ceildiv(cp.y0, cp.comps[c].dy), d->reduce));
+                if ((int)p.width == cw && (int)p.height == chh) { sx = cp.comps[c].dx; sy = cp.comps[c].dy; }
+            }
+            launch_copy_channel(d->d_out, S, d->ncomp, c, cp.comps[0].sgnd, d->outW, (int)p.width, (int)p.height, sx, sy, d->d_stage + offs[c], cc, d->st);
         }
         CK(cudaMemcpyAsync(d->h_out, d->d_stage, stage, cudaMemcpyDeviceToHost, d->st));
         CK(stream_wait(d->st, d->ev_wait));
@@ -581,7 +645,7 @@ int j2kcuda_stage_t1_decode(const uint8_t* data, const int32_t* blk, int nblk, i
     for (auto& b : hb) b.coeff = d_out + (uintptr_t)b.coeff;
     CK(cudaMemcpy(d_seg, arena.data(), arena.size(), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(d_blk, hb.data(), sizeof(T1DecBlock) * nblk, cudaMemcpyHostToDevice));
-    launch_t1_decode(d_blk, nblk, d_seg, 1, 0);
+    launch_t1_decode(d_blk, nblk, d_seg, nullptr, 0, 1, 0);
     cudaError_t e = cudaDeviceSynchronize();
     if (e == cudaSuccess) e = cudaMemcpy(out, d_out, outn * 4, cudaMemcpyDeviceToHost);
     cudaFree(d_out); cudaFree(d_seg); cudaFree(d_blk);

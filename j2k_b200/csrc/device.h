@@ -46,8 +46,18 @@ struct PixelDst {
 void launch_mct_inverse(const PixelDst& dst, const MctParams& mp, const int32_t* const planes[4], cudaStream_t st);
 // decode side of CopyBuffer for a destination that is not the tight image the inverse MCT kernel writes: component c of
 // the tight interleaved image `img` (S-byte samples, signed when sgnd) -> a tight w x h plane of the caller's sample type
-void launch_copy_channel(const uint8_t* img, int S, int ncomp, int c, int sgnd, int img_w, int w, int h, uint8_t* dst,
+// (sx, sy: read every sx-th / sy-th sample of the image: a destination at a sub-sampled component's own resolution)
+void launch_copy_channel(const uint8_t* img, int S, int ncomp, int c, int sgnd, int img_w, int w, int h, int sx, int sy, uint8_t* dst,
                          const CopyConv& conv, cudaStream_t st);
+// Output stage when some components are sub-sampled (no MCT then): level shift, clamp, and every component replicated to the
+// reference grid -- output sample (x, y) of component c = its plane at (x / dx, y / dy), the rule of Codec::CopyBuffer
+// (src/common/j2k_codec.cpp:262-279: the source advances once every relativeSub destination samples).
+struct SubOut {
+    const int32_t* plane[4];
+    int dx[4], dy[4], cw[4], ch[4], prec[4], dc_shift[4];
+    int width, height, pitch, ncomp, sample_bytes, irreversible, sgnd;
+};
+void launch_output_subsampled(const SubOut& so, uint8_t* d_out, cudaStream_t st);
 // bare three-plane transforms used by the stage entry points (mct.cpp:94-471)
 void launch_mct_planes(int32_t* c0, int32_t* c1, int32_t* c2, size_t n, int irreversible, int inverse, cudaStream_t st);
 
@@ -118,10 +128,16 @@ struct T1DecBlock {            // decode job, one code-block
     uint8_t npasses;
     uint32_t data_off, data_len;   // into the segment arena
     float stepsize;            // 9/7 dequantiser step, already halved (tcd.cpp:888)
+    uint32_t seg_index;        // first entry of the block's codeword segments in the segment table (when nsegs > 1)
+    uint16_t nsegs;            // codeword segments (1 unless the code-block style terminates passes: TERMALL, LAZY)
+    uint8_t cblksty;           // code-block style bits of the component (j2k.h:77-82)
+    uint8_t roishift;          // region-of-interest up-shift of the component (RGN marker)
     uint32_t pad;
 };
-void launch_t1_decode(const T1DecBlock* d_blocks, int nblocks, const uint8_t* seg_arena, int raw_output,
-                      cudaStream_t st);
+struct T1DecSeg { uint32_t off, len, passes, pad; };   // one codeword segment: bytes at off in the segment arena (8-byte aligned, 0xFF 0xFF after)
+// generic = 1: some block uses a code-block style, several segments or an ROI shift (slower kernel variant)
+void launch_t1_decode(const T1DecBlock* d_blocks, int nblocks, const uint8_t* seg_arena, const T1DecSeg* d_segs, int generic,
+                      int raw_output, cudaStream_t st);
 
 const char* device_tables_init();   // uploads LUTs once per device; returns error text or null
 

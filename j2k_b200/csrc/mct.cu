@@ -222,17 +222,33 @@ __global__ void __launch_bounds__(256) k_mct_inverse(const InvArgs a) {
 }
 
 __global__ void __launch_bounds__(256) k_copy_channel(const uint8_t* __restrict__ img, int S, int ncomp, int c, int sgnd, int img_w, int w, int h,
-                                                      uint8_t* __restrict__ dst, const CopyConv cc) {
+                                                      int sx, int sy, uint8_t* __restrict__ dst, const CopyConv cc) {
     const long long total = (long long)w * h;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const int y = (int)(i / w), x = (int)(i % w);
-        const uint8_t* p = img + (((long long)y * img_w + x) * ncomp + c) * S;
+        const uint8_t* p = img + (((long long)y * sy * img_w + (long long)x * sx) * ncomp + c) * S;
         long long s = S == 1 ? (sgnd ? (long long)*reinterpret_cast<const int8_t*>(p) : (long long)*p)
                              : (sgnd ? (long long)*reinterpret_cast<const int16_t*>(p) : (long long)*reinterpret_cast<const uint16_t*>(p));
         const long long r = cc.plain ? s : copy_convert(s, cc);
         if (cc.dst_type == 0) dst[i] = (uint8_t)r;
         else if (cc.dst_type == 1) reinterpret_cast<uint16_t*>(dst)[i] = (uint16_t)r;
         else reinterpret_cast<uint32_t*>(dst)[i] = (uint32_t)r;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_output_subsampled(const SubOut a, uint8_t* __restrict__ out) {
+    const long long total = (long long)a.width * a.height;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int y = (int)(i / a.width), x = (int)(i % a.width);
+        for (int c = 0; c < a.ncomp; ++c) {
+            const int xs = min(x / a.dx[c], a.cw[c] - 1), ys = min(y / a.dy[c], a.ch[c] - 1);
+            int v = a.plane[c][(long long)ys * a.pitch + xs];
+            if (a.irreversible) v = (int)lrintf(__int_as_float(v));
+            const int lo = a.sgnd ? -(1 << (a.prec[c] - 1)) : 0, hi = a.sgnd ? (1 << (a.prec[c] - 1)) - 1 : (1 << a.prec[c]) - 1;
+            v = min(max(v + a.dc_shift[c], lo), hi);
+            uint8_t* p = out + (i * a.ncomp + c) * a.sample_bytes;
+            if (a.sample_bytes == 1) *p = (uint8_t)v; else *reinterpret_cast<uint16_t*>(p) = (uint16_t)v;
+        }
     }
 }
 
@@ -313,10 +329,15 @@ void launch_mct_inverse(const PixelDst& dst, const MctParams& mp, const int32_t*
     MCT_DISPATCH(k_mct_inverse, a, dst.sample_bytes, a.nch, grid, st);
 }
 
-void launch_copy_channel(const uint8_t* img, int S, int ncomp, int c, int sgnd, int img_w, int w, int h, uint8_t* dst,
+void launch_copy_channel(const uint8_t* img, int S, int ncomp, int c, int sgnd, int img_w, int w, int h, int sx, int sy, uint8_t* dst,
                          const CopyConv& conv, cudaStream_t st) {
     if (w <= 0 || h <= 0) return;
-    k_copy_channel<<<grid_for((long long)w * h), 256, 0, st>>>(img, S, ncomp, c, sgnd, img_w, w, h, dst, conv);
+    k_copy_channel<<<grid_for((long long)w * h), 256, 0, st>>>(img, S, ncomp, c, sgnd, img_w, w, h, sx, sy, dst, conv);
+}
+
+void launch_output_subsampled(const SubOut& so, uint8_t* d_out, cudaStream_t st) {
+    if (so.width <= 0 || so.height <= 0) return;
+    k_output_subsampled<<<grid_for((long long)so.width * so.height), 256, 0, st>>>(so, d_out);
 }
 
 void launch_mct_planes(int32_t* c0, int32_t* c1, int32_t* c2, size_t n, int irreversible, int inverse, cudaStream_t st) {

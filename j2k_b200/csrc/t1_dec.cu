@@ -18,10 +18,10 @@ namespace {
 using namespace t1dec;
 constexpr int DEC_WARPS = 4;
 
-template <int MINB>
+template <int MINB, bool GEN>
 __global__ void __launch_bounds__(32 * DEC_WARPS, MINB)
 k_t1_decode(const T1DecBlock* __restrict__ blocks, int nblocks, const T1Tables* __restrict__ tab,
-            const uint8_t* __restrict__ seg_arena, int raw_output) {
+            const uint8_t* __restrict__ seg_arena, const T1DecSeg* __restrict__ segtab, int raw_output) {
     __shared__ DRows s_rows[DEC_WARPS];
     __shared__ ColBuf s_cols[DEC_WARPS];
     __shared__ uint32_t s_state[DEC_WARPS][32];
@@ -51,22 +51,25 @@ k_t1_decode(const T1DecBlock* __restrict__ blocks, int nblocks, const T1Tables* 
     uint32_t* st = s_state[warp];
     if (lane < T1_NCTX) st[lane] = s_mq[lane == CTX_UNI ? 46 * 2 : (lane == CTX_AGG ? 3 * 2 : (lane == CTX_ZC ? 4 * 2 : 0))];
     __syncwarp();
-    decode_block(blk, R, s_cols[warp], &s_io[warp], st, s_zc, s_sc, s_mq, seg_arena, raw_output, lane, 32);
+    decode_block<GEN>(blk, R, s_cols[warp], &s_io[warp], st, s_zc, s_sc, s_mq, seg_arena, segtab, raw_output, lane, 32);
 }
 
 }  // namespace
 
-void launch_t1_decode(const T1DecBlock* d_blocks, int nblocks, const uint8_t* seg_arena, int raw_output, cudaStream_t st) {
+void launch_t1_decode(const T1DecBlock* d_blocks, int nblocks, const uint8_t* seg_arena, const T1DecSeg* d_segs, int generic,
+                      int raw_output, cudaStream_t st) {
     if (nblocks <= 0) return;
-    // register budget / occupancy trade-off, tunable for experiments: 4 -> 108 regs (16 warps/SM), 5 -> 96 (20, the
-    // default: best with several frames in flight), 6 -> 80 (24)
+    // register budget / occupancy trade-off, tunable for experiments: 4 -> 111 regs (16 warps/SM), 5 -> 96 (20), 6 -> 80 (24, the
+    // default: best with several frames in flight), 7 -> 72 (28), 8 -> 64 (32)
     static const int variant = [] { const char* e = getenv("J2KCUDA_DEC_MINB"); return e ? atoi(e) : 6; }();
     const dim3 grid((nblocks + DEC_WARPS - 1) / DEC_WARPS), block(32 * DEC_WARPS);
-    if (variant <= 4) k_t1_decode<4><<<grid, block, 0, st>>>(d_blocks, nblocks, t1_tables_device(), seg_arena, raw_output);
-    else if (variant == 5) k_t1_decode<5><<<grid, block, 0, st>>>(d_blocks, nblocks, t1_tables_device(), seg_arena, raw_output);
-    else if (variant == 6) k_t1_decode<6><<<grid, block, 0, st>>>(d_blocks, nblocks, t1_tables_device(), seg_arena, raw_output);
-    else if (variant == 7) k_t1_decode<7><<<grid, block, 0, st>>>(d_blocks, nblocks, t1_tables_device(), seg_arena, raw_output);
-    else k_t1_decode<8><<<grid, block, 0, st>>>(d_blocks, nblocks, t1_tables_device(), seg_arena, raw_output);
+    const T1Tables* tab = t1_tables_device();
+    if (generic) { k_t1_decode<4, true><<<grid, block, 0, st>>>(d_blocks, nblocks, tab, seg_arena, d_segs, raw_output); return; }
+    if (variant <= 4) k_t1_decode<4, false><<<grid, block, 0, st>>>(d_blocks, nblocks, tab, seg_arena, d_segs, raw_output);
+    else if (variant == 5) k_t1_decode<5, false><<<grid, block, 0, st>>>(d_blocks, nblocks, tab, seg_arena, d_segs, raw_output);
+    else if (variant == 6) k_t1_decode<6, false><<<grid, block, 0, st>>>(d_blocks, nblocks, tab, seg_arena, d_segs, raw_output);
+    else if (variant == 7) k_t1_decode<7, false><<<grid, block, 0, st>>>(d_blocks, nblocks, tab, seg_arena, d_segs, raw_output);
+    else k_t1_decode<8, false><<<grid, block, 0, st>>>(d_blocks, nblocks, tab, seg_arena, d_segs, raw_output);
 }
 
 }  // namespace j2k

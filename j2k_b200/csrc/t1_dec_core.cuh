@@ -227,27 +227,69 @@ J2K_HD inline uint32_t spread4(uint32_t n) {
 // Decode one code-block.  Called by all `nlanes` lanes of a warp with identical arguments except `lane`;
 // the decision loop runs redundantly on warp-uniform data, the lane index only partitions the
 // column-parallel parts (stripe set-up and write-back, fold, final pass).  R and st must be zero / reset on entry.
+// Raw ("lazy", selective arithmetic coding bypass) bit reader: raw.cpp:91-117.  A byte that follows 0xFF carries 7 bits.
+struct RawDec {
+    const uint8_t* p; uint32_t len, pos, c, ct;
+    J2K_HD inline void init(const uint8_t* data, uint32_t n) { p = data; len = n; pos = 0; c = 0; ct = 0; }
+    J2K_HD inline uint32_t get() {
+        if (ct == 0) {
+            ct = 8;
+            if (pos == len) c = 0xff;
+            else { if (c == 0xff) ct = 7; c = p[pos++]; }
+        }
+        --ct;
+        return (c >> ct) & 1u;
+    }
+};
+enum { CBLK_LAZY = 1, CBLK_RESET = 2, CBLK_TERMALL = 4, CBLK_VSC = 8, CBLK_PTERM = 16, CBLK_SEGSYM = 32 };   // j2k.h:77-82
+
+J2K_HD inline void reset_contexts(uint32_t* st, const uint32_t* mqtab, int lane, int nlanes) {     // t1.cpp:1391-1394
+    for (int i = lane; i < T1_NCTX; i += nlanes)
+        st[i] = mqtab[i == CTX_UNI ? 46 * 2 : (i == CTX_AGG ? 3 * 2 : (i == CTX_ZC ? 4 * 2 : 0))];
+    J2K_SYNCWARP();
+}
+
+// GEN = false: the plain coder (cblksty == 0, one codeword segment, no region of interest) -- what every configuration of
+// the encoder writes.  GEN = true adds what foreign streams may use (t1.cpp:1337-1448): several segments per block
+// (TERMALL, LAZY), raw passes (LAZY, raw.cpp), context reset after every pass (RESET), vertically causal contexts (VSC),
+// the segmentation symbol (SEGSYM) and the ROI down-shift (T1Decoder.cpp:59-76).
+template <bool GEN>
 J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, MqIo* io, uint32_t* st, const uint8_t* zc_all, const uint8_t* sc,
-                                const uint32_t* mqtab, const uint8_t* seg_arena, int raw_output, int lane, int nlanes) {
+                                const uint32_t* mqtab, const uint8_t* seg_arena, const T1DecSeg* segtab, int raw_output, int lane, int nlanes) {
     const int w = blk.w, h = blk.h;
     int32_t* out = blk.coeff;
     const uint8_t* zc = zc_all + blk.orient * 512;
     const int nstripes = (h + 3) >> 2;
     const u64 colmask = w == 64 ? ~0ull : ((1ull << w) - 1);
+    const int sty = GEN ? blk.cblksty : 0;
+    const bool vsc = GEN && (sty & CBLK_VSC);
 
     MqDec mq;
-    mq.init(io, seg_arena + blk.data_off);
+    RawDec rawd;
+    bool raw = false;
+    int segno = 0, seg_left = blk.npasses;
+    if (!GEN) mq.init(io, seg_arena + blk.data_off);
+    else { seg_left = 0; segno = -1; rawd.init(seg_arena, 0); }
 
-    int bp = blk.numbps - 1;              // 0-based bit-plane being decoded
+    int bp = blk.numbps + (GEN ? blk.roishift : 0) - 1;              // 0-based bit-plane being decoded
     int passtype = 2;
     int lastplane = bp;
     bool firstfold = true;
     for (int passno = 0; passno < blk.npasses && bp >= 0; ++passno) {
+        if (GEN && seg_left == 0) {                  // next codeword segment: restart the MQ decoder or the raw reader on its bytes
+            ++segno;
+            const T1DecSeg sg = blk.nsegs > 1 ? segtab[blk.seg_index + segno] : T1DecSeg{blk.data_off, blk.data_len, blk.npasses, 0};
+            seg_left = (int)sg.passes;
+            raw = (sty & CBLK_LAZY) && bp + 1 <= (int)blk.numbps - 4 && passtype < 2;
+            if (raw) rawd.init(seg_arena + sg.off, sg.len); else mq.init(io, seg_arena + sg.off);
+            J2K_SYNCWARP();
+        }
         for (int sidx = 0; sidx < nstripes; ++sidx) {
             const int ib = 4 * sidx;       // smem index of row q = 0
             u64 S[6], V[4], valid[4];
 #pragma unroll
             for (int q = 0; q < 6; ++q) S[q] = R.sig[ib + q];
+            if (vsc) S[5] = 0;                       // vertically causal: the stripe below does not exist for the contexts
 #pragma unroll
             for (int r = 0; r < 4; ++r) { V[r] = R.vis[ib + 1 + r]; valid[r] = (ib + r < h) ? colmask : 0ull; }
             // ---- which columns can hold anything to decode in this pass ----
@@ -286,6 +328,7 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, MqI
                     u64 G[6];
 #pragma unroll
                     for (int q = 0; q < 6; ++q) G[q] = R.sgn[ib + q];
+                    if (vsc) G[5] = 0;
                     cb.gwin[x] = pack_win(G, x);
                 }
                 uint32_t a = nibble(memb, x);
@@ -336,14 +379,19 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, MqI
                         const int r = J2K_FFSLL(todo) - 1;
                         todo &= todo - 1;
                         const uint32_t s9 = (win >> (3 * r)) & 0x1ffu;
-                        if (!mq.decode(st, mqtab, zc[s9 & 0x1efu])) continue;
+                        if (GEN && raw) { if (!rawd.get()) continue; }
+                        else if (!mq.decode(st, mqtab, zc[s9 & 0x1efu])) continue;
                         if (!have_g) {
                             gwin = cb.gwin[x];
                             if (x == carry_x + 1) gwin |= spread4(carry_g);
                             have_g = true;
                         }
-                        const uint32_t e = sc[sc_index(s9, (gwin >> (3 * r)) & 0x1ffu)];
-                        const uint32_t neg = mq.decode(st, mqtab, CTX_SC + (e & 7u)) ^ (e >> 3);
+                        uint32_t neg;
+                        if (GEN && raw) neg = rawd.get();          // the sign itself, no context (t1.cpp:396-399)
+                        else {
+                            const uint32_t e = sc[sc_index(s9, (gwin >> (3 * r)) & 0x1ffu)];
+                            neg = mq.decode(st, mqtab, CTX_SC + (e & 7u)) ^ (e >> 3);
+                        }
                         win |= 2u << (3 * r + 3);
                         gwin |= (neg << 1) << (3 * r + 3);
                         new4 |= 1u << r; neg4 |= neg << r;
@@ -370,7 +418,8 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, MqI
                     c32 &= c32 - 1;
                     uint32_t list = cb.aux[x] >> 8, res = 0, k = 0;
                     do {
-                        res |= mq.decode_cached(st, mqtab, CTX_MAG - 1 + (list & 3u), mr_lc, mr_le) << k;
+                        if (GEN && raw) res |= rawd.get() << k;
+                        else res |= mq.decode_cached(st, mqtab, CTX_MAG - 1 + (list & 3u), mr_lc, mr_le) << k;
                         ++k; list >>= 2;
                     } while (list);
                     if (res) { cb.out[x] = res; any = true; }
@@ -460,6 +509,11 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, MqI
             J2K_SYNCWARP();
         }
         lastplane = bp;
+        if (GEN) {
+            if (passtype == 2 && (sty & CBLK_SEGSYM)) for (int k = 0; k < 4; ++k) mq.decode(st, mqtab, CTX_UNI);   // t1.cpp:1099-1111
+            if ((sty & CBLK_RESET) && !raw) { J2K_SYNCWARP(); reset_contexts(st, mqtab, lane, nlanes); }
+            --seg_left;
+        }
         if (++passtype == 3 || passno + 1 == blk.npasses) {
             // fold this plane's decoded bits into the magnitudes kept in the coefficient plane
             const bool plane_done = passtype == 3;
@@ -503,7 +557,8 @@ J2K_HD inline void decode_block(const T1DecBlock& blk, DRows& R, ColBuf& cb, MqI
             if ((sg >> x) & 1ull) {
                 const int32_t m = firstfold ? 0 : *p;
                 const int qlast = ((la >> x) & 1ull) ? lastplane : lastplane + 1;
-                const int32_t t1 = (m << 1) | (1 << qlast);          // one extra fractional bit, t1.cpp:419-445
+                int32_t t1 = (m << 1) | (1 << qlast);                // one extra fractional bit, t1.cpp:419-445
+                if (GEN && blk.roishift && t1 >= (1 << blk.roishift)) t1 >>= blk.roishift;    // T1Decoder.cpp:59-76
                 v = ((ng >> x) & 1ull) ? -t1 : t1;
             }
             if (raw_output) *p = v;

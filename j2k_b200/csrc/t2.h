@@ -103,7 +103,9 @@ bool join_tile_streams(const CodingParams& cp, const uint8_t* const* frags, cons
                        ByteBuf& out, std::string& err);
 
 // ---- decoder side ---------------------------------------------------------------------------
+struct DecSeg { int numpasses = 0, maxpasses = 109, len = 0; };   // opj_tcd_seg_t, t2.cpp:1525-1563
 struct DecBlock {
+    std::vector<DecSeg> segs;  // codeword segments (one unless the code-block style terminates passes)
     int numbps = 0;
     int npasses = 0;          // total passes over all layers read
     int numlenbits = 3;

@@ -183,7 +183,14 @@ bool DecoderHost::parse_main_header(const uint8_t* d, size_t n, size_t& pos, std
             }
             break;
         }
-        case 0xff5e: err = "ROI (RGN) is not supported"; return false;
+        case 0xff5e: {                                                   // RGN, j2k.cpp:3998-4075: implicit ROI up-shift per component
+            if (!have_siz) { err = "RGN before SIZ"; return false; }
+            if (L < 5) { err = "bad RGN"; return false; }
+            const uint32_t c = r.u(cp.ncomp <= 256 ? 1 : 2), style = r.u(1), shift = r.u(1);
+            if ((int)c >= cp.ncomp || style != 0 || shift > 30) { err = "bad RGN"; return false; }
+            cp.comps[c].roishift = (int)shift;
+            break;
+        }
         default: break;                                                  // TLM, PLM, PPM(!), CRG, COM ...
         }
         if (m == 0xff60) { err = "packed packet headers (PPM) are not supported"; return false; }
@@ -194,7 +201,7 @@ bool DecoderHost::parse_main_header(const uint8_t* d, size_t n, size_t& pos, std
     for (int c = 0; c < cp.ncomp; ++c) {
         const CompParams& t = cp.comps[c];
         if (t.numres < 1 || t.numres > MAX_RES || t.cblkw > 10 || t.cblkh > 10 || t.cblkw + t.cblkh > 12) { err = "bad coding style"; return false; }
-        if (t.cblksty != 0) { err = "code-block style switches (bypass/reset/termall/vsc/pterm/segsym) are not supported"; return false; }
+        if (t.cblksty & ~0x3f) { err = "unknown code-block style bits"; return false; }
     }
     pos = r.pos;
     return true;
@@ -262,10 +269,30 @@ static bool read_packet(const CodingParams& cp, DecTile& t, const PacketId& pk, 
                 int incr = 0;
                 while (bio.getbit()) { if (++incr > 32) { err = "bad Lblock"; return false; } }
                 cb.numlenbits += incr;
-                const int nbits = cb.numlenbits + floorlog2((uint32_t)np);
-                if (nbits > 31) { err = "bad segment length field"; return false; }     // a 32-bit length used to wrap to -1
-                const uint32_t len = bio.read(nbits);
-                if (len > end - pos) { err = "code-block segment longer than the tile-part"; return false; }
+                // codeword segments (t2.cpp:1262-1295, 1525-1563): TERMALL ends one after every pass, LAZY after the first ten
+                // passes and then after every two / one; otherwise the block is one segment
+                const int sty = cp.comps[pk.compno].cblksty;
+                auto new_seg = [&](bool first) {
+                    DecSeg sg;
+                    if (sty & 4) sg.maxpasses = 1;
+                    else if (sty & 1) sg.maxpasses = first ? 10 : ((cb.segs.back().maxpasses == 1 || cb.segs.back().maxpasses == 10) ? 2 : 1);
+                    cb.segs.push_back(sg);
+                };
+                if (cb.segs.empty()) new_seg(true);
+                else if (cb.segs.back().numpasses == cb.segs.back().maxpasses) new_seg(false);
+                uint32_t len = 0;
+                for (int n = np; n > 0;) {
+                    DecSeg& sg = cb.segs.back();
+                    const int take = std::min(sg.maxpasses - sg.numpasses, n);
+                    const int nbits = cb.numlenbits + floorlog2((uint32_t)take);
+                    if (nbits > 31) { err = "bad segment length field"; return false; }     // a 32-bit length used to wrap to -1
+                    const uint32_t sl = bio.read(nbits);
+                    if (sl > end - pos || len + sl > end - pos) { err = "code-block segment longer than the tile-part"; return false; }
+                    sg.numpasses += take; sg.len += (int)sl;
+                    len += sl;
+                    n -= take;
+                    if (n > 0) { if (cb.segs.size() > 200) { err = "too many codeword segments"; return false; } new_seg(false); }
+                }
                 cb.npasses += np;
                 if (ninc < 4096) inc[ninc++] = Inc{prc.first_cblk + k, len};
                 else big.push_back(Inc{prc.first_cblk + k, len});
@@ -310,7 +337,7 @@ bool DecoderHost::parse(const uint8_t* d, size_t n, std::string& err) {
     else
         for (auto& t : tiles) {
             t.parts.clear();
-            for (auto& b : t.blocks) { b.numbps = 0; b.npasses = 0; b.numlenbits = 3; b.included = false; b.chunks.clear(); b.len = 0; }
+            for (auto& b : t.blocks) { b.numbps = 0; b.npasses = 0; b.numlenbits = 3; b.included = false; b.chunks.clear(); b.len = 0; b.segs.clear(); }
             for (auto& tr : t.incl) tr.reset();
             for (auto& tr : t.imsb) tr.reset();
         }

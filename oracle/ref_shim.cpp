@@ -348,7 +348,9 @@ int ref_t1_encode_cblk_generic(const int32_t* coeff, int w, int h, int stride, i
 {
     opj_t1_t* t1 = opj_t1_create(true, 0, 0);
     if (!t1 || !opj_t1_allocate_buffers(t1, w, h)) return 1;
-    t1->data_stride = w;                                  /* encoder layout, t1.cpp:1496 */
+    std::vector<int32_t> plane((size_t)w * h);
+    t1->data = plane.data();                              /* the encoder codes straight from the tile buffer (t1.cpp:1496): here a copy */
+    t1->data_stride = w;
     uint32_t max = 0;
     for (int j = 0; j < h; ++j)
         for (int i = 0; i < w; ++i) {

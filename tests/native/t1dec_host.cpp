@@ -30,7 +30,7 @@ extern "C" int t1dec_host_block(const uint8_t* data, int len, int w, int h, int 
     uint8_t sc2[256];
     for (int i = 0; i < 256; ++i) sc2[i] = sc_entry(sc, i);
     static MqIo io;
-    decode_block(b, R, cb, &io, st, zc9, sc2, tab, seg.data(), 1, 0, 1);
+    decode_block<false>(b, R, cb, &io, st, zc9, sc2, tab, seg.data(), nullptr, 1, 0, 1);
     return 0;
 }
 
@@ -40,4 +40,44 @@ extern "C" void copyconv_host(const int64_t* src, int64_t* dst, int n, int src_t
                               int dst_depth, int dst_sgnd) {
     const j2k::CopyConv c = j2k::make_copy_conv(src_type, src_depth, src_sgnd, dst_type, dst_depth, dst_sgnd);
     for (int i = 0; i < n; ++i) dst[i] = c.plain ? j2k::cb_as(dst_type, src[i]) : j2k::copy_convert(src[i], c);
+}
+
+// ---- the generic variant (code-block styles, several codeword segments, ROI shift): decode_block<true> ----
+extern "C" int t1dec_host_block_gen(const uint8_t* data, const int* seg_len, const int* seg_passes, int nsegs, int w, int h, int orient,
+                                    int numbps, int cblksty, int roishift, const uint8_t* zc9, const uint8_t* sc, const uint32_t* mq, int32_t* out) {
+    std::vector<uint64_t> arena64;
+    std::vector<T1DecSeg> segs;
+    size_t total = 0;
+    for (int i = 0; i < nsegs; ++i) total += ((size_t)seg_len[i] + 2 + 7) / 8 + 1;
+    arena64.assign(total + 8, ~0ull);
+    uint8_t* arena = reinterpret_cast<uint8_t*>(arena64.data());
+    size_t pos = 0, in = 0;
+    int npasses = 0;
+    for (int i = 0; i < nsegs; ++i) {
+        memcpy(arena + pos, data + in, (size_t)seg_len[i]);
+        segs.push_back(T1DecSeg{(uint32_t)pos, (uint32_t)seg_len[i], (uint32_t)seg_passes[i], 0});
+        in += (size_t)seg_len[i]; npasses += seg_passes[i];
+        pos += (((size_t)seg_len[i] + 2) + 7) & ~(size_t)7;
+    }
+    T1DecBlock b;
+    memset(&b, 0, sizeof(b));
+    b.coeff = out; b.pitch = w; b.w = (uint16_t)w; b.h = (uint16_t)h; b.orient = (uint8_t)orient; b.qmfbid = 1;
+    b.numbps = (uint8_t)numbps; b.npasses = (uint8_t)npasses; b.stepsize = 1.f;
+    b.data_off = segs.empty() ? 0 : segs[0].off; b.data_len = segs.empty() ? 0 : segs[0].len;
+    b.nsegs = (uint16_t)nsegs; b.seg_index = 0; b.cblksty = (uint8_t)cblksty; b.roishift = (uint8_t)roishift;
+    memset(out, 0, sizeof(int32_t) * (size_t)w * h);
+    if (!npasses || !numbps || !w || !h) return 0;
+    static DRows R;
+    memset(&R, 0, sizeof(R));
+    uint32_t tab[96];
+    for (int i = 0; i < 94; ++i) tab[i] = mq_state_word(mq, i);
+    uint32_t st[32];
+    for (int i = 0; i < 32; ++i) st[i] = tab[0];
+    st[CTX_UNI] = tab[46 * 2]; st[CTX_AGG] = tab[3 * 2]; st[CTX_ZC] = tab[4 * 2];
+    static ColBuf cb;
+    static MqIo io;
+    uint8_t sc2[256];
+    for (int i = 0; i < 256; ++i) sc2[i] = sc_entry(sc, i);
+    decode_block<true>(b, R, cb, &io, st, zc9, sc2, tab, arena, segs.data(), 1, 0, 1);
+    return 0;
 }

@@ -169,3 +169,22 @@ def t1_encode_cblk_generic(coeff, orient, cblksty):
     total = rates[n - 1] if n else 0
     return dict(data=out[:total].tobytes(), numbps=numbps.value, npasses=n, rates=[rates[i] for i in range(n)],
                 lens=[lens[i] for i in range(n)], terms=[terms[i] for i in range(n)])
+
+
+def decode_components(data, reduce=0, threads=1):
+    """like decode(), for streams whose components 1.. are sub-sampled: -> list of arrays, each at its component's own size"""
+    inf = probe(data)
+    dx, dy = C.c_int(1), C.c_int(1)
+    lib().ref_last_subsampling(C.byref(dx), C.byref(dy))
+    w = -(-inf["w"] // (1 << reduce)); h = -(-inf["h"] // (1 << reduce))
+    planes = [np.zeros((h, w), dtype=np.int32) for _ in range(inf["ncomp"])]
+    info = (C.c_int * 5)()
+    rc = lib().ref_decode(data, C.c_size_t(len(data)), reduce, threads, _planes_ptr(planes), len(planes), info)
+    if rc != 0:
+        raise RuntimeError("ref_decode failed rc=%d" % rc)
+    out = [planes[0]]
+    for c in range(1, inf["ncomp"]):
+        cw = -(-(-(-inf["w"] // dx.value)) // (1 << reduce))         # ceildivpow2(ceildiv(W, dx), reduce)
+        chh = -(-(-(-inf["h"] // dy.value)) // (1 << reduce))
+        out.append(planes[c].ravel()[:cw * chh].reshape(chh, cw).copy())
+    return out
