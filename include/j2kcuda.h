@@ -298,10 +298,21 @@ typedef struct j2kcuda_block_result {
     const double* dist;
 } j2kcuda_block_result;
 int j2kcuda_t2_block_count(const j2kcuda_params* p);
+/* The other direction of the same hand-off: the DEVICE results of every code-block of the frame a context has just run
+ * (after j2kcuda_encoder_run), in the same order; returns the number of blocks or -1.  rates as above, dist cumulative.
+ * Valid until the next upload / run on the context.  What integration/grok_plugin.cpp fills opj_plugin_tile_t from
+ * (openjpeg.h:1308-1360). */
+int j2kcuda_encoder_block_results(j2kcuda_encoder* e, j2kcuda_block_result* out, int max_blocks);
+/* DWT coefficients of one component after j2kcuda_encoder_run, in the reference's in-place Mallat tile buffer layout
+ * (width x height int32): the image data grok's OPJ_PLUGIN_STATE_DEBUG_ENCODE cross-check expects.  Single-tile frames. */
+int j2kcuda_encoder_download_coefficients(j2kcuda_encoder* e, int comp, int32_t* out);
 /* Geometry of every code-block in that order, 12 int32 per block: tile, comp, x, y (position in the
  * tile-component's Mallat plane), w, h, orient, level (numres-1-resno), band numbps, bandconst
  * (t1.cpp:1482), band stepsize (float32 bits), resno.  Returns blocks written.  (tcd.cpp:592-842) */
 int j2kcuda_t2_block_geometry(const j2kcuda_params* p, int32_t* geo, int max_blocks);
+/* 8 int32 per block, same order: band index within its resolution, precinct index, index within the precinct, precincts of the
+ * resolution (empty ones included), bounds in band coordinates x0, y0, x1, y1. */
+int j2kcuda_t2_block_structure(const j2kcuda_params* p, int32_t* out, int max_blocks);
 int j2kcuda_t2_assemble(const j2kcuda_params* p, const j2kcuda_block_result* blocks, int nblocks,
                         uint8_t** out, size_t* out_len);
 /* Host Tier-2 parse alone: returns, per code-block in the same order, numbps, npasses, len and

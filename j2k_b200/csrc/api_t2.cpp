@@ -64,6 +64,34 @@ int j2kcuda_t2_block_geometry(const j2kcuda_params* p, int32_t* geo, int max_blo
     return n;
 }); }
 
+// Where each code-block sits in the tile -> component -> resolution -> band -> precinct hierarchy (tcd.cpp:592-842), 8 int32 per
+// block in the order of j2kcuda_t2_block_geometry: band index within the resolution, precinct index, block index within the
+// precinct, precincts of the resolution (pw * ph, empty ones included), then the block's bounds in band coordinates
+// x0, y0, x1, y1.  What a filler of grok's opj_plugin_tile_t needs (openjpeg.h:1308-1360).
+int j2kcuda_t2_block_structure(const j2kcuda_params* p, int32_t* out, int max_blocks) { return j2k::guarded([&]() -> int {
+    if (!p || !out) return -1;
+    if (const char* why = check_params(*p)) { set_error(J2KCUDA_ERR_PARAM, why); return -1; }
+    CodingParams cp;
+    setup_coding_params(*p, cp);
+    int n = 0;
+    for (int t = 0; t < (int)(cp.tw * cp.th); ++t) {
+        if (!cp.tile_in_range(t)) continue;
+        TileGeo g;
+        build_tile(cp, t, 1.0f, g);
+        for (size_t k = 0; k < g.cblks.size(); ++k) {
+            if (n >= max_blocks) return n;
+            const CblkGeo& cb = g.cblks[k];
+            const ResGeo& rg = g.comps[cb.comp].res[cb.res];
+            const PrecGeo& pg = rg.bands[cb.band].precs[cb.prec];
+            int32_t* o = out + 8 * (size_t)n;
+            o[0] = cb.band; o[1] = cb.prec; o[2] = (int32_t)k - pg.first_cblk; o[3] = rg.pw * rg.ph;
+            o[4] = cb.r.x0; o[5] = cb.r.y0; o[6] = cb.r.x1; o[7] = cb.r.y1;
+            ++n;
+        }
+    }
+    return n;
+}); }
+
 int j2kcuda_t2_assemble(const j2kcuda_params* p, const j2kcuda_block_result* blocks, int nblocks,
                         uint8_t** out, size_t* out_len) { return j2k::guarded([&]() -> int {
     if (!p || !blocks || !out || !out_len) return set_error(J2KCUDA_ERR_PARAM, "null argument");

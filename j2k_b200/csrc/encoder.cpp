@@ -328,6 +328,37 @@ static int upload_planes(j2kcuda_encoder* e, const j2kcuda_plane* planes, int np
     return J2KCUDA_OK;
 }
 
+// Per code-block results of the last run, in Tier-2 order: the cumulative weighted distortion of every pass
+// (t1_opt.cpp:711-722 with t1.cpp:1114-1143, in double and in pass order like the reference) and the block's bytes / rates.
+static void fill_block_results(j2kcuda_encoder* e) {
+    const CodingParams& cp = e->cp;
+    for (int i = 0; i < e->nblocks; ++i) {
+        const T1Result& r = e->h_results[i];
+        EncTile& tile = e->tiles[e->blk_tile[i]];
+        const CblkGeo& cb = tile.geo.cblks[e->blk_index[i]];
+        const BandGeo& band = tile.geo.comps[cb.comp].res[cb.res].bands[cb.band];
+        EncBlock& b = tile.blocks[e->blk_index[i]];
+        const bool real = cp.comps[cb.comp].qmfbid == 0;
+        const int level = cp.comps[cb.comp].numres - 1 - cb.res;
+        const double w1 = (cp.mct && cb.comp < 3 && cp.ncomp >= 3) ? mct_norm(cb.comp, real) : 1.0;
+        const double w2 = dwt_norm(level, cb.orient, real);
+        std::vector<double>& d = e->dist[i];
+        d.resize(r.npasses + 1);
+        double cum = 0;
+        int bpno = r.numbps - 1, passtype = 2;
+        for (int k = 0; k < r.npasses; ++k) {
+            double w = w1 * w2 * (double)band.stepsize * (double)(1 << bpno);
+            w *= w * r.nmsedec[k] / 8192.0;
+            cum += w;
+            d[k] = cum;
+            if (++passtype == 3) { passtype = 0; --bpno; }
+        }
+        b.data = e->h_packed + e->h_offsets[i];
+        b.numbps = r.numbps; b.totalpasses = r.npasses;
+        b.rates = r.rate; b.dist = d.data();
+    }
+}
+
 // ---- contexts kept between one-shot calls (WriteFile after WriteFile with the same settings) ----
 namespace {
 std::mutex g_pool_mu;
@@ -491,32 +522,7 @@ int j2kcuda_encoder_finish(j2kcuda_encoder* e, uint8_t** out, size_t* out_len) {
         }
         tile.distotile = 0; tile.packno = 0;
     }
-    for (int i = 0; i < e->nblocks; ++i) {
-        const T1Result& r = e->h_results[i];
-        EncTile& tile = e->tiles[e->blk_tile[i]];
-        const CblkGeo& cb = tile.geo.cblks[e->blk_index[i]];
-        const BandGeo& band = tile.geo.comps[cb.comp].res[cb.res].bands[cb.band];
-        EncBlock& b = tile.blocks[e->blk_index[i]];
-        // cumulative weighted distortion, t1_opt.cpp:711-722 with t1.cpp:1114-1143
-        const bool real = cp.comps[cb.comp].qmfbid == 0;
-        const int level = cp.comps[cb.comp].numres - 1 - cb.res;
-        const double w1 = (cp.mct && cb.comp < 3 && cp.ncomp >= 3) ? mct_norm(cb.comp, real) : 1.0;
-        const double w2 = dwt_norm(level, cb.orient, real);
-        std::vector<double>& d = e->dist[i];
-        d.resize(r.npasses + 1);
-        double cum = 0;
-        int bpno = r.numbps - 1, passtype = 2;
-        for (int k = 0; k < r.npasses; ++k) {
-            double w = w1 * w2 * (double)band.stepsize * (double)(1 << bpno);
-            w *= w * r.nmsedec[k] / 8192.0;
-            cum += w;
-            d[k] = cum;
-            if (++passtype == 3) { passtype = 0; --bpno; }
-        }
-        b.data = e->h_packed + e->h_offsets[i];
-        b.numbps = r.numbps; b.totalpasses = r.npasses;
-        b.rates = r.rate; b.dist = d.data();
-    }
+    fill_block_results(e);
     EncoderHost host;
     host.cp = cp;
     host.ntiles = (int)e->tiles.size();
@@ -526,6 +532,46 @@ int j2kcuda_encoder_finish(j2kcuda_encoder* e, uint8_t** out, size_t* out_len) {
     *out_len = cs.size();
     *out = cs.release();
     e->ms[6] = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    return J2KCUDA_OK;
+}); }
+
+// What grok's accelerator hand-off needs (plugin_bridge.cpp:72-174, openjpeg.h:1308-1360): the device results of every
+// code-block after j2kcuda_encoder_run, in Tier-2 order.  The pointers stay valid until the next upload / run on this context.
+int j2kcuda_encoder_block_results(j2kcuda_encoder* e, j2kcuda_block_result* out, int max_blocks) { return j2k::guarded([&]() -> int {
+    if (!e || !out) { set_error(J2KCUDA_ERR_PARAM, "null argument"); return -1; }
+    if (!e->ran) { set_error(J2KCUDA_ERR_PARAM, "encoder_run has not completed"); return -1; }
+    if (max_blocks < e->nblocks) { set_error(J2KCUDA_ERR_PARAM, "block array too small"); return -1; }
+    fill_block_results(e);
+    for (int i = 0; i < e->nblocks; ++i) {
+        const EncBlock& b = e->tiles[e->blk_tile[i]].blocks[e->blk_index[i]];
+        out[i].data = b.data; out[i].numbps = b.numbps; out[i].npasses = b.totalpasses; out[i].rates = b.rates; out[i].dist = b.dist;
+    }
+    return e->nblocks;
+}); }
+
+// The DWT coefficients of one component after j2kcuda_encoder_run, assembled into the reference's single in-place tile buffer
+// (Mallat layout, tile_buf.cpp:147-157): grok's OPJ_PLUGIN_STATE_DEBUG_ENCODE cross-check wants them as the image data
+// (tcd.cpp:1042-1079).  out = width x height int32, row-major.  Single-tile frames only.
+int j2kcuda_encoder_download_coefficients(j2kcuda_encoder* e, int comp, int32_t* out) { return j2k::guarded([&]() -> int {
+    if (!e || !out || comp < 0 || comp >= e->ncomp) return set_error(J2KCUDA_ERR_PARAM, "bad argument");
+    if (!e->ran) return set_error(J2KCUDA_ERR_PARAM, "encoder_run has not completed");
+    if (e->tiles.size() != 1) return set_error(J2KCUDA_ERR_UNSUPPORTED, "coefficient download is for single-tile frames");
+    CK(cudaSetDevice(e->device));
+    const CompGeo& cg = e->tiles[0].geo.comps[comp];
+    const int levels = e->numres - 1;
+    for (int r = 0; r < e->numres; ++r) {
+        const ResGeo& rg = cg.res[r];
+        for (int b = 0; b < rg.numbands; ++b) {
+            const BandGeo& bg = rg.bands[b];
+            if (bg.r.w() <= 0 || bg.r.h() <= 0) continue;
+            const int level = r == 0 ? levels : e->numres - r;              // decomposition level whose output holds the band
+            const int32_t* plane = levels == 0 ? e->planeA[comp] : ((level & 1) ? e->planeB[comp] : e->planeA[comp]);
+            const int32_t* src = plane + (size_t)(cg.r.y0 + bg.offy) * e->pitch + (cg.r.x0 + bg.offx);
+            CK(cudaMemcpy2DAsync(out + (size_t)bg.offy * e->W + bg.offx, (size_t)e->W * 4, src, (size_t)e->pitch * 4, (size_t)bg.r.w() * 4, (size_t)bg.r.h(),
+                                 cudaMemcpyDeviceToHost, e->st));
+        }
+    }
+    CK(stream_wait(e->st, e->ev_wait));
     return J2KCUDA_OK;
 }); }
 

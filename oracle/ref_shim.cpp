@@ -379,4 +379,66 @@ int ref_t1_encode_cblk_generic(const int32_t* coeff, int w, int h, int stride, i
     return 0;
 }
 
+/* ---- the accelerator path of the reference (openjpeg.cpp:1077-1160): load a plug-in, let it encode `infile`, and finish the
+ * codestream with opj_encode_with_plugin in the callback, as bin/jp2/opj_compress.cpp:1526-1630 does.  Returns 0 and the bytes. */
+static MemOut* g_plugin_out = NULL;
+static int g_plugin_rc = 0;
+static void plugin_cb(opj_plugin_encode_user_callback_info_t* info) {
+    g_plugin_rc = 10;
+    opj_codec_t* codec = opj_create_compress(OPJ_CODEC_J2K);
+    opj_stream_t* stream = opj_stream_create(1 << 20, false);
+    if (codec && stream) {
+        opj_stream_set_user_data(stream, g_plugin_out, NULL);
+        opj_stream_set_read_function(stream, mo_read);
+        opj_stream_set_write_function(stream, mo_write);
+        opj_stream_set_skip_function(stream, mo_skip);
+        opj_stream_set_seek_function(stream, mo_seek);
+        opj_set_error_handler(codec, msg_cb, NULL);
+        opj_set_warning_handler(codec, msg_cb, NULL);
+        opj_set_info_handler(codec, quiet_cb, NULL);
+        if (opj_setup_encoder(codec, info->encoder_parameters, info->image) && opj_start_compress(codec, info->image, stream) &&
+            opj_encode_with_plugin(codec, info->tile, stream) && opj_end_compress(codec, stream))
+            g_plugin_rc = 0;
+    }
+    if (stream) opj_stream_destroy(stream);
+    if (codec) opj_destroy_codec(codec);
+    info->error_code = g_plugin_rc;
+}
+int ref_encode_with_plugin(const char* plugin_path, const char* infile, const ref_params* p, uint8_t* out, size_t cap, size_t* out_len)
+{
+    static bool loaded = false;
+    if (!loaded) {
+        opj_plugin_init_info_t pi;
+        pi.plugin_path = plugin_path;
+        if (!opj_plugin_init(pi)) return 1;
+        loaded = true;
+    }
+    opj_cparameters_t params;
+    opj_set_default_encoder_parameters(&params);
+    params.irreversible = p->irreversible;
+    if (p->numresolution > 0) params.numresolution = p->numresolution;
+    if (p->cblockw > 0) params.cblockw_init = p->cblockw;
+    if (p->cblockh > 0) params.cblockh_init = p->cblockh;
+    params.tcp_mct = (uint8_t)p->tcp_mct;
+    params.prog_order = (OPJ_PROG_ORDER)p->prog_order;
+    params.tcp_numlayers = p->numlayers;
+    params.cp_disto_alloc = p->disto_alloc;
+    for (int i = 0; i < 8; ++i) params.tcp_rates[i] = p->rates[i];
+    if (p->rsiz) { params.rsiz = (uint16_t)p->rsiz; params.max_comp_size = p->max_comp_size; params.max_cs_size = p->max_cs_size; }
+    params.numThreads = p->num_threads > 0 ? p->num_threads : 1;
+    strncpy(params.infile, infile, sizeof(params.infile) - 1);
+    params.outfile[0] = 0;
+    params.cod_format = 0;
+    MemOut mo;
+    g_plugin_out = &mo;
+    g_plugin_rc = 11;
+    int32_t rc = opj_plugin_encode(&params, plugin_cb);
+    g_plugin_out = NULL;
+    if (rc || g_plugin_rc) return 20 + (rc ? 1 : 0) + g_plugin_rc;
+    *out_len = mo.buf.size();
+    if (mo.buf.size() > cap) return 3;
+    memcpy(out, mo.buf.data(), mo.buf.size());
+    return 0;
+}
+
 } /* extern "C" */

@@ -188,3 +188,18 @@ def decode_components(data, reduce=0, threads=1):
         chh = -(-(-(-inf["h"] // dy.value)) // (1 << reduce))
         out.append(planes[c].ravel()[:cw * chh].reshape(chh, cw).copy())
     return out
+
+
+def encode_with_plugin(plugin_path, infile, irreversible=0, numresolution=6, cblk=(64, 64), mct=0, prog=0, numlayers=1, disto_alloc=1,
+                       rsiz=0, max_comp_size=0, max_cs_size=0, rates=()):
+    """the reference's accelerator path: opj_plugin_init + opj_plugin_encode + opj_encode_with_plugin (openjpeg.cpp:1077-1160)"""
+    p = RefParams(irreversible, numresolution, cblk[0], cblk[1], mct, prog, 0, 0, numlayers, disto_alloc, rsiz, max_comp_size, max_cs_size, 1)
+    for i, r in enumerate(rates):
+        p.rates[i] = r
+    cap = 64 << 20
+    out = np.empty(cap, dtype=np.uint8)
+    n = C.c_size_t(0)
+    rc = lib().ref_encode_with_plugin(plugin_path.encode(), infile.encode(), C.byref(p), C.c_void_p(out.ctypes.data), C.c_size_t(cap), C.byref(n))
+    if rc != 0:
+        raise RuntimeError("ref_encode_with_plugin failed rc=%d" % rc)
+    return out[:n.value].tobytes()
