@@ -121,6 +121,10 @@ int j2kcuda_encode(const j2kcuda_params* p, const j2kcuda_plane* planes, int npl
 int j2kcuda_decode(const uint8_t* bytes, size_t n, unsigned reduce, const j2kcuda_plane* planes,
                    int nplanes, j2kcuda_abort_fn abort_fn, void* user);
 
+/* j2kcuda_decode restricted to a window (see j2kcuda_decoder_set_window) */
+int j2kcuda_decode_region(const uint8_t* bytes, size_t n, unsigned reduce, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1,
+                          const j2kcuda_plane* planes, int nplanes);
+
 /* ---- persistent contexts (image sequences: configs C4/C5; also what bench.py times) -------- */
 typedef struct j2kcuda_encoder j2kcuda_encoder;
 typedef struct j2kcuda_decoder j2kcuda_decoder;
@@ -149,6 +153,11 @@ j2kcuda_decoder* j2kcuda_decoder_create(int device);
 void j2kcuda_decoder_destroy(j2kcuda_decoder* d);
 /* host Tier-2 parse + H2D of code-block segments */
 int j2kcuda_decoder_prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned reduce);
+/* decode window, opj_set_decode_area (openjpeg.h:1287-1302; dwt_region.cpp, tile_buf.cpp:233-340): only [x0, x1) x [y0, y1)
+ * of the reference grid (full-resolution coordinates) is wanted by the next prepare / run / download: code-blocks that cannot
+ * reach it through the synthesis filters are skipped, the planes receive the window (sized ceil of it at `reduce`).
+ * x1 == y1 == 0: whole image again. */
+int j2kcuda_decoder_set_window(j2kcuda_decoder* d, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1);
 /* device stages: T1 decode, dequantise, inverse DWT, inverse MCT, level shift, clamp */
 int j2kcuda_decoder_run(j2kcuda_decoder* d);
 /* device -> host planes */
@@ -160,6 +169,7 @@ int j2kcuda_decoder_get_device_output(j2kcuda_decoder* d, void** d_pixels, int64
 int j2kcuda_decoder_copy_to_device(j2kcuda_decoder* d, void* d_pixels, int64_t pitch_bytes);
 /* [0] host tier-2 parse (wall) [1] H2D [2] t1 [3] idwt [4] imct+pack [5] D2H [6] idwt finest level */
 int j2kcuda_decoder_timings(j2kcuda_decoder* d, float* ms, int n);
+/* [0] kernels launched [1] code-blocks [2] code-blocks skipped by the decode window [3] codestream bytes [4] h2d bytes [5] output bytes */
 int j2kcuda_decoder_counters(j2kcuda_decoder* d, uint64_t* v, int n);
 
 /* ---- sequences: frames of an image sequence on this process's device (one process per GPU;

@@ -45,6 +45,9 @@ struct j2kcuda_decoder {
     T1DecSeg* d_segs = nullptr; size_t d_segs_cap = 0;
     bool generic = false;                                                     // some block needs the generic Tier-1 variant
     bool subsampled = false;                                                  // some component has dx or dy != 1
+    // decode window in reference-grid coordinates at full resolution (opj_set_decode_area); x1 == 0: the whole image
+    uint32_t win_x0 = 0, win_y0 = 0, win_x1 = 0, win_y1 = 0;
+    uint64_t blocks_skipped = 0;
     T1DecBlock* d_blocks = nullptr; size_t d_blocks_cap = 0;
     uint8_t* h_seg = nullptr; size_t h_seg_cap = 0;                           // pinned
     uint8_t* d_seg = nullptr; size_t d_seg_cap = 0;
@@ -152,7 +155,7 @@ static int prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned 
     // ---- block table + segment arena ----
     const int levels = d->numres - 1;
     const int maxres = d->numres - 1 - (int)reduce;
-    d->h_blocks.clear(); d->h_segs.clear();
+    d->h_blocks.clear(); d->h_segs.clear(); d->blocks_skipped = 0;
     bool generic = false;
     size_t seg = 0;
     for (auto& t : d->host.tiles)
@@ -183,8 +186,22 @@ static int prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned 
         for (size_t k = 0; k < g.cblks.size(); ++k) {
             const CblkGeo& cb = g.cblks[k];
             if (cb.res > maxres) continue;
-            const DecBlock& db = t.blocks[k];
+            DecBlock& db = t.blocks[k];
             const CompGeo& cg = g.comps[cb.comp];
+            if (d->win_x1 && db.included) {
+                // Decode window (dwt_region.cpp, tile_buf.cpp:233-340): a code-block whose samples cannot reach the window
+                // through the synthesis filters is left at zero.  A sample of decomposition level n sits on a 2^n grid; the
+                // inverse transform spreads it over fewer than 3 * 2^n (5/3) / 6 * 2^n (9/7) reference-grid samples per side.
+                const int n = cb.res == 0 ? levels : d->numres - cb.res;
+                const int64_t m = (int64_t)(cp.comps[cb.comp].qmfbid ? 3 : 6) << n;
+                const int64_t dx = cp.comps[cb.comp].dx, dy = cp.comps[cb.comp].dy;
+                const int64_t bx0 = (((int64_t)cb.r.x0 << n) - m) * dx, bx1 = (((int64_t)cb.r.x1 << n) + m) * dx;
+                const int64_t by0 = (((int64_t)cb.r.y0 << n) - m) * dy, by1 = (((int64_t)cb.r.y1 << n) + m) * dy;
+                if (bx1 <= (int64_t)d->win_x0 || bx0 >= (int64_t)d->win_x1 || by1 <= (int64_t)d->win_y0 || by0 >= (int64_t)d->win_y1) {
+                    db.included = false; db.npasses = 0; db.len = 0; db.chunks.clear(); db.segs.clear();
+                    ++d->blocks_skipped;
+                }
+            }
             const BandGeo& band = cg.res[cb.res].bands[cb.band];
             T1DecBlock b;
             memset(&b, 0, sizeof(b));
@@ -264,7 +281,7 @@ static int prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, unsigned 
     if (!all.empty()) CK(cudaMemcpyAsync(d->d_jobs, all.data(), all.size() * sizeof(DwtJob), cudaMemcpyHostToDevice, d->st));
     CK(cudaEventRecord(d->ev[1], d->st));
     CK(stream_wait(d->st, d->ev_wait));          // h_blocks / all are pageable host vectors
-    d->counters[1] = nblk; d->counters[3] = (uint64_t)len;
+    d->counters[1] = nblk; d->counters[2] = d->blocks_skipped; d->counters[3] = (uint64_t)len;
     d->counters[4] = seg + d->h_blocks.size() * sizeof(T1DecBlock) + all.size() * sizeof(DwtJob);
     d->prepared = true; d->ran = false;
     return J2KCUDA_OK;
@@ -368,6 +385,20 @@ static int download(j2kcuda_decoder* d, const j2kcuda_plane* planes, int nplanes
                 p.colbytes == (int64_t)d->ncomp * S && p.rowbytes == (int64_t)d->outW * d->ncomp * S &&
                 (int)p.width == d->outW && (int)p.height == d->outH && depth == cp.comps[c].prec && !p.sgnd == !cp.comps[c].sgnd;
     }
+    // decode window: the planes receive the window's samples (its top-left sample first), cut out of the full image on the device
+    size_t win_off = 0;
+    int win_w = d->outW, win_h = d->outH;
+    if (d->win_x1) {
+        const int ix0 = (int)ceildivpow2(cp.x0, d->reduce), iy0 = (int)ceildivpow2(cp.y0, d->reduce);
+        const int wx0 = std::max((int)ceildivpow2(d->win_x0, d->reduce) - ix0, 0), wy0 = std::max((int)ceildivpow2(d->win_y0, d->reduce) - iy0, 0);
+        const int wx1 = std::min((int)ceildivpow2(d->win_x1, d->reduce) - ix0, d->outW), wy1 = std::min((int)ceildivpow2(d->win_y1, d->reduce) - iy0, d->outH);
+        if (wx1 <= wx0 || wy1 <= wy0) return set_error(J2KCUDA_ERR_PARAM, "decode window lies outside the image");
+        win_off = ((size_t)wy0 * d->outW + wx0) * d->ncomp * S;
+        win_w = wx1 - wx0; win_h = wy1 - wy0;
+        for (int c = 0; c < nc; ++c)
+            if ((int)planes[c].width > win_w || (int)planes[c].height > win_h) return set_error(J2KCUDA_ERR_PARAM, "destination plane larger than the decode window");
+        tight = false;
+    }
     CK(cudaEventRecord(d->ev[7], d->st));
     if (d->host.tile_count) {
         // this context decoded a range of the frame's tiles (the others are on other GPUs): their rectangles go straight
@@ -446,7 +477,7 @@ static int download(j2kcuda_decoder* d, const j2kcuda_plane* planes, int nplanes
                 const int chh = (int)(ceildivpow2(ceildiv(cp.y1, cp.comps[c].dy), d->reduce) - ceildivpow2(ceildiv(cp.y0, cp.comps[c].dy), d->reduce));
                 if ((int)p.width == cw && (int)p.height == chh) { sx = cp.comps[c].dx; sy = cp.comps[c].dy; }
             }
-            launch_copy_channel(d->d_out, S, d->ncomp, c, cp.comps[0].sgnd, d->outW, (int)p.width, (int)p.height, sx, sy, d->d_stage + offs[c], cc, d->st);
+            launch_copy_channel(d->d_out + win_off, S, d->ncomp, c, cp.comps[0].sgnd, d->outW, (int)p.width, (int)p.height, sx, sy, d->d_stage + offs[c], cc, d->st);
         }
         CK(cudaMemcpyAsync(d->h_out, d->d_stage, stage, cudaMemcpyDeviceToHost, d->st));
         CK(stream_wait(d->st, d->ev_wait));
@@ -528,6 +559,15 @@ int j2kcuda_decoder_prepare(j2kcuda_decoder* d, const uint8_t* bytes, size_t n, 
     d->prepared = false;
     return prepare(d, bytes, n, reduce);
 }); }
+// opj_set_decode_area (openjpeg.h:1287-1302): only the rectangle [x0, x1) x [y0, y1) of the reference grid (full-resolution
+// coordinates) is wanted; code-blocks that cannot influence it are not decoded.  x1 == 0 && y1 == 0 resets to the whole image.
+int j2kcuda_decoder_set_window(j2kcuda_decoder* d, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1) { return j2k::guarded([&]() -> int {
+    if (!d) return set_error(J2KCUDA_ERR_PARAM, "null decoder");
+    if ((x1 || y1) && (x1 <= x0 || y1 <= y0)) return set_error(J2KCUDA_ERR_PARAM, "empty decode window");
+    d->win_x0 = x0; d->win_y0 = y0; d->win_x1 = x1; d->win_y1 = y1;
+    return J2KCUDA_OK;
+}); }
+
 int j2kcuda_decoder_run(j2kcuda_decoder* d) { return j2k::guarded([&]() -> int { return d ? run(d) : set_error(J2KCUDA_ERR_PARAM, "null decoder"); }); }
 int j2kcuda_decoder_download(j2kcuda_decoder* d, const j2kcuda_plane* planes, int nplanes) { return j2k::guarded([&]() -> int {
     if (!d || !planes) return set_error(J2KCUDA_ERR_PARAM, "null argument");
@@ -577,6 +617,22 @@ int j2kcuda_decode(const uint8_t* bytes, size_t n, unsigned reduce, const j2kcud
     if (!rc && abort_fn && abort_fn(user)) rc = set_error(J2KCUDA_ERR_ABORTED, "aborted by the caller");
     if (!rc) rc = j2kcuda_decoder_run(d);
     if (!rc) rc = j2kcuda_decoder_download(d, planes, nplanes);
+    if (rc == J2KCUDA_ERR_CUDA) j2kcuda_decoder_destroy(d); else pool_give(d);
+    return rc;
+}); }
+
+int j2kcuda_decode_region(const uint8_t* bytes, size_t n, unsigned reduce, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1,
+                          const j2kcuda_plane* planes, int nplanes) { return j2k::guarded([&]() -> int {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return set_error(J2KCUDA_ERR_NO_DEVICE, "no CUDA device: libj2kcuda has no CPU path"); }
+    j2kcuda_decoder* d = pool_take(dev);
+    if (!d) d = j2kcuda_decoder_create(-1);
+    if (!d) return J2KCUDA_ERR_NO_DEVICE;
+    int rc = j2kcuda_decoder_set_window(d, x0, y0, x1, y1);
+    if (!rc) rc = j2kcuda_decoder_prepare(d, bytes, n, reduce);
+    if (!rc) rc = j2kcuda_decoder_run(d);
+    if (!rc) rc = j2kcuda_decoder_download(d, planes, nplanes);
+    j2kcuda_decoder_set_window(d, 0, 0, 0, 0);
     if (rc == J2KCUDA_ERR_CUDA) j2kcuda_decoder_destroy(d); else pool_give(d);
     return rc;
 }); }

@@ -6,6 +6,7 @@ import pytest
 import orc
 import j2k
 import refgrok
+from j2k_b200 import _lib as L
 from j2k_b200.frames import make_frame
 
 pytestmark = pytest.mark.gpu
@@ -102,3 +103,35 @@ def test_4k_rgba16_roundtrip():
     img = make_frame(2160, 4096, 4, 16, "smooth", seed=9)
     cs = j2k.encode(img, 16, mct=1)
     assert np.array_equal(j2k.decode(cs), img)
+
+
+# ---- decode windows (row f3, second half): opj_set_decode_area ----
+@pytest.mark.gpu
+@pytest.mark.parametrize("irreversible,tile,reduce", [(0, 0, 0), (1, 0, 0), (0, 128, 0), (0, 0, 1), (1, 128, 2)])
+@pytest.mark.parametrize("win", [(0, 0, 64, 48), (301, 97, 420, 203), (250, 0, 512, 30), (100, 300, 101, 301)])
+def test_decode_window_equals_the_crop_of_the_full_decode(irreversible, tile, reduce, win):
+    import ctypes as C
+    img = make_frame(384, 512, 3, 8, "noise", seed=17)
+    cs = j2k.encode(img, 8, mct=1, irreversible=irreversible, tile_w=tile, tile_h=tile, numresolution=5)
+    full = j2k.decode(cs, reduce=reduce)
+    x0, y0, x1, y1 = win
+    f = 1 << reduce
+    rx0, ry0, rx1, ry1 = -(-x0 // f), -(-y0 // f), -(-x1 // f), -(-y1 // f)
+    if rx1 <= rx0 or ry1 <= ry0:
+        return
+    out = np.zeros((ry1 - ry0, rx1 - rx0, 3), np.uint8)
+    lib = L.lib()
+    d = C.c_void_p(lib.j2kcuda_decoder_create(-1))
+    assert lib.j2kcuda_decoder_set_window(d, x0, y0, x1, y1) == 0
+    assert lib.j2kcuda_decoder_prepare(d, cs, C.c_size_t(len(cs)), reduce) == 0, L.last_error()
+    assert lib.j2kcuda_decoder_run(d) == 0, L.last_error()
+    assert lib.j2kcuda_decoder_download(d, j2k.planes_of(out), 3) == 0, L.last_error()
+    cnt = (C.c_uint64 * 6)()
+    lib.j2kcuda_decoder_counters(d, cnt, 6)
+    lib.j2kcuda_decoder_destroy(d)
+    assert np.array_equal(out, full[ry0:ry1, rx0:rx1])
+    if (x1 - x0) * (y1 - y0) < 20000:
+        assert cnt[2] > cnt[1] // 3                                  # a small window skips most of the Tier-1 work
+    out2 = np.zeros_like(out)
+    assert lib.j2kcuda_decode_region(cs, C.c_size_t(len(cs)), reduce, x0, y0, x1, y1, j2k.planes_of(out2), 3) == 0, L.last_error()
+    assert np.array_equal(out2, out)
