@@ -124,7 +124,7 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--kind", default="smooth", choices=["smooth", "noise", "ramp"])
     ap.add_argument("--frames", type=int, default=FRAMES)
-    ap.add_argument("--workers", type=int, default=WORKERS)
+    ap.add_argument("--workers", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -133,6 +133,10 @@ def main():
     if args.impl == "reference":
         run_reference(args, rank)
         return
+    if args.workers <= 0:
+        # frames in flight per GPU: enough to keep the Tier-1 kernels of several frames on the device while other frames are in
+        # host Tier-2, but no more host threads than the box has cores for (8 ranks x 16 workers on 32 cores cost 20 % at N = 8)
+        args.workers = max(6, min(WORKERS, (os.cpu_count() or 16) // max(world, 1)))
 
     import torch
     import torch.distributed as dist
@@ -292,6 +296,70 @@ def main():
         return float(t.item())
 
     t_pipe = pipelined()
+
+    # the stress content class: uniform noise, every bit-plane of every block coded -- Tier-1 works ~3.4 x longer per
+    # frame than on the smooth frames of the headline; two timed steps of the same F-frame batch, device-resident
+    def noise_value():
+        nf = min(F, 8)
+        nd = []
+        for f in range(nf):
+            t = torch.empty((H, W, NC), dtype=torch.uint16).pin_memory()
+            t.numpy()[...] = make_frame(H, W, NC, PREC, "noise", seed=1000 + rank * nf + f)
+            nd.append(t.cuda())
+        nb = [torch.empty((H, W, NC), dtype=torch.uint16, device="cuda") for _ in range(nf)]
+        tin, _ka = dev_table(nd)
+        tout, _kb = dev_table(nb)
+        o = (C.POINTER(C.c_uint8) * nf)(); l = (C.c_size_t * nf)()
+
+        def one():
+            if lib.j2kcuda_sequence_encode(seq, tin, nf, NC, 1, o, l):
+                raise SystemExit("noise encode failed: " + L.last_error())
+            if lib.j2kcuda_sequence_decode(seq, C.cast(o, C.POINTER(C.POINTER(C.c_uint8))), l, nf, 0, tout, NC, 1):
+                raise SystemExit("noise decode failed: " + L.last_error())
+            for i in range(nf):
+                lib.j2kcuda_free(o[i])
+        one()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(2):
+            one()
+        e1.record()
+        torch.cuda.synchronize()
+        for i in range(nf):
+            if not torch.equal(nb[i], nd[i]):
+                raise SystemExit("noise round trip of frame %d is not lossless" % i)
+        t = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return world * 2 * nf * W * H / (float(t.item()) * 1e-3) / 1e6, nf
+
+    v_noise, nf_noise = noise_value()
+
+    # the plug-in's situation: ONE frame at a time through the one-shot calls the j2k::Codec binding makes (j2kcuda_encode /
+    # j2kcuda_decode, contexts kept by the library between calls), from and to PAGEABLE memory
+    def pageable_single():
+        img = np.ascontiguousarray(host[0].numpy().copy())           # pageable copy
+        out = np.zeros_like(img)
+        pl_in, pl_out = j2k.planes_of(img), j2k.planes_of(out)
+        te, td = [], []
+        for i in range(4):
+            o = C.POINTER(C.c_uint8)(); n = C.c_size_t(0)
+            t0 = time.perf_counter()
+            if lib.j2kcuda_encode(C.byref(p), pl_in, NC, C.byref(o), C.byref(n)):
+                raise SystemExit("one-shot encode failed: " + L.last_error())
+            t1 = time.perf_counter()
+            if lib.j2kcuda_decode(o, n, 0, pl_out, NC, None, None):
+                raise SystemExit("one-shot decode failed: " + L.last_error())
+            t2 = time.perf_counter()
+            lib.j2kcuda_free(o)
+            if i:
+                te.append(t1 - t0); td.append(t2 - t1)
+        if not np.array_equal(out, img):
+            raise SystemExit("one-shot round trip is not lossless")
+        return min(te) * 1e3, min(td) * 1e3
+
+    enc_ms_page, dec_ms_page = pageable_single() if rank == 0 else (0.0, 0.0)
     sampler.stop = True
     sampler.join(timeout=3)
     lib.j2kcuda_sequence_destroy(seq)
@@ -321,6 +389,7 @@ def main():
     e2e = world * args.steps * F * mpix / (t_e2e * 1e-3)
     peak, peak_src = peaks()
     l1_bytes = 8.0 * W * H * NC                      # 4 B read + 4 B written per sample, level 1 of every component
+    all_bytes = float(sum(8 * NC * (-(-W // (1 << l))) * (-(-H // (1 << l))) for l in range(5)))     # levels 1..5 of a 6-resolution transform
     l1_ms = float(solo_enc[7])
     achieved = l1_bytes / (l1_ms * 1e-3) / 1e9
     l1_ms_batch = float(em_b[7]) / nfr
@@ -348,7 +417,16 @@ def main():
                      "how": "library CUDA events on the context's stream around the launch, one frame at a time after the timed region",
                      "in_batch": {"avg_launch_ms": l1_ms_batch, "achieved": l1_bytes / (l1_ms_batch * 1e-3) / 1e9,
                                   "note": "same launch inside the timed region, sharing the device with the Tier-1 kernels of the other frames in flight"},
-                     "inverse_level1": {"avg_launch_ms": il1_ms, "achieved": l1_bytes / (il1_ms * 1e-3) / 1e9}},
+                     "inverse_level1": {"avg_launch_ms": il1_ms, "achieved": l1_bytes / (il1_ms * 1e-3) / 1e9},
+                     "all_levels": {"algorithmic_bytes": all_bytes,
+                                    "forward": {"ms": float(solo_enc[2]), "achieved": all_bytes / (float(solo_enc[2]) * 1e-3) / 1e9, "frac": all_bytes / (float(solo_enc[2]) * 1e-3) / 1e9 / peak},
+                                    "inverse": {"ms": float(solo_dec[3]), "achieved": all_bytes / (float(solo_dec[3]) * 1e-3) / 1e9, "frac": all_bytes / (float(solo_dec[3]) * 1e-3) / 1e9 / peak},
+                                    "note": "BASELINE.md 4: 8 B per sample of every level's input region, all five launches of one frame (CUDA events around them, frame alone)"},
+                     "traffic_source": "profiles/r1_roundtrip_full_raw.csv (ncu --set full, commit 03157f7; the level-1 kernels are unchanged since)"},
+        "value_noise": {"value": v_noise, "unit": "MPix/s", "frames_per_step_per_gpu": nf_noise,
+                        "note": "same round trip on uniform-noise frames (every bit-plane of every code-block coded): the stress figure beside the smooth-frame headline"},
+        "e2e_pageable": {"value": W * H / ((enc_ms_page + dec_ms_page) * 1e-3) / 1e6, "unit": "MPix/s", "encode_ms": enc_ms_page, "decode_ms": dec_ms_page,
+                         "note": "ONE frame at a time through j2kcuda_encode + j2kcuda_decode (what the j2k::Codec binding calls) from and to pageable host memory; contexts cached by the library"},
         "stages_ms_per_frame_alone": {k: float(v) for k, v in zip(enc_names, solo_enc)},
         "decode_stages_ms_per_frame_alone": {k: float(v) for k, v in zip(dec_names, solo_dec)},
         "stages_ms_per_frame_in_batch": {k: float(v) / nfr for k, v in zip(enc_names, em_b)},

@@ -18,4 +18,14 @@ decprof)   # ncu full capture of the Tier-1 decode kernel of one 4K frame: tools
   env "$@" ncu --set full --clock-control none --import-source on -k regex:k_t1_decode -s 2 -c 1 -f -o gpurun_out/$name \
       python tools/dec_bench.py --frames 1 --alone-only --tag $name > gpurun_out/${name}_ncu.log 2>&1
   cat gpurun_out/${name}_plain.log; tail -3 gpurun_out/${name}_ncu.log ;;
+dwtsweep)  # per-level tunables of the DWT kernels (J2KCUDA_DWT_*), forward and inverse totals of one 4K RGBA16 frame
+  : > gpurun_out/dwtsweep.log
+  for cfg in "" "J2KCUDA_DWT_MINSP=4" "J2KCUDA_DWT_MINSP=2" "J2KCUDA_DWT_MINSP=4 J2KCUDA_DWT_FLOOR=4736" "J2KCUDA_DWT_MINSP=4 J2KCUDA_DWT_FLOOR=9472" \
+             "J2KCUDA_DWT_PF=2" "J2KCUDA_DWT_PF=3" "J2KCUDA_DWT_PF_INV=3" "J2KCUDA_DWT_PF_INV=1" "J2KCUDA_DWT_NCOL=8" "J2KCUDA_DWT_NCOL=8 J2KCUDA_DWT_PF=2" \
+             "J2KCUDA_DWT_ITEMS=9472" "J2KCUDA_DWT_ITEMS=28416" "J2KCUDA_DWT_MINSP=4 J2KCUDA_DWT_PF=2 J2KCUDA_DWT_PF_INV=3"; do
+    echo "== $cfg" >> gpurun_out/dwtsweep.log
+    env $cfg python tools/stage_times.py dwt 2>&1 | grep -E "mct=|dwt_l1" >> gpurun_out/dwtsweep.log
+    env $cfg python tools/stage_times.py decode1 2>&1 | grep -E "idwt" >> gpurun_out/dwtsweep.log
+  done
+  cat gpurun_out/dwtsweep.log ;;
 esac

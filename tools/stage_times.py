@@ -76,6 +76,8 @@ if __name__ == "__main__":
             run_decode(2160, 4096, 3, 12, kind, irreversible=1, mct=1, profile=L.PROFILE_CINEMA_4K)
     elif "dwt" in sys.argv:
         run(2160, 4096, 4, 16, "smooth", reps=6, mct=1)
+    elif "decode1" in sys.argv:
+        run_decode(2160, 4096, 4, 16, "smooth", mct=1)
     elif "decode" in sys.argv:
         for kind in ("smooth", "noise"):
             run_decode(2160, 4096, 4, 16, kind, mct=1)
