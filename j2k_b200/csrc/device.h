@@ -75,6 +75,26 @@ struct DwtJob {
     int pad;
 };
 enum { DWT_53 = 0, DWT_97_FIX = 1, DWT_97_FLOAT = 2 };
+// Level 1 of the forward transform fused with sample unpacking, DC level shift and RCT / ICT: one job per tile, all components
+// at once, straight from the caller's interleaved pixels (dwt.cu).  Used when the source is an interleaved 1- or 2-byte image
+// with 3 or 4 channels per pixel whose samples need no depth / sign conversion.
+struct DwtPxSrc {             // per frame: where the pixels are
+    const uint8_t* px;        // sample (0, 0) of channel 0 of the interleaved image on the device
+    long long rowbytes;
+    int chan[4];              // channel of component c inside a pixel
+};
+struct DwtPxJob {             // per context: fixed geometry
+    int32_t* dst[4];          // Mallat region origin of every component
+    int x0, y0, x1, y1, pitch;
+    int strip0, nstrips, nsegs, strip_cols;
+    int dc[4];
+    int mct, irreversible;
+};
+bool dwt_px_fusion_available();
+bool launch_dwt_forward_px(const DwtPxJob* d_jobs, const DwtPxSrc& src, int njobs, int max_items, int kind, int ncomp, int nch, int sample_bytes,
+                           cudaStream_t st);
+// interleave detection shared with the MCT kernels: channels per pixel (0 = not one interleaved array), chan[c] = channel of component c
+int detect_pixel_interleave(const PixelSrc& s, int ncomp, int chan[4]);
 // host-side helper: fills strip/segment counts (jobs[i].strip0 = row pairs per segment, the same
 // for all jobs of the launch); returns the largest number of warp work items of any job
 int dwt_plan_jobs(DwtJob* jobs, int njobs);

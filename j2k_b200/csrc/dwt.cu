@@ -338,6 +338,167 @@ k_dwt_forward(const DwtJob* __restrict__ jobs) {
     else forward_rows<L, N, PF, false>(src, dst, c);
 }
 
+// ---- level 1 fused with sample unpacking, DC level shift and RCT / ICT ---------------------------------------------------
+// The first decomposition level reads the caller's interleaved pixels directly (2 or 1 bytes per sample instead of the 4-byte
+// planes the separate MCT kernel would have written and this kernel read back): per row a lane takes its four pixels with
+// 16/8/4-byte loads, applies the level shift and the component transform in registers (tcd.cpp:1659-1696, mct.cpp:94-157,
+// 241-401) and feeds NC vertical lifting recurrences at once.  Everything after the load is the code of k_dwt_forward.
+
+__device__ __forceinline__ int fm13(int a, int b) { return (int)(((long long)a * (long long)b + 4096) >> 13); }
+
+template <int S> __device__ __forceinline__ int px_sample(const uint32_t* w, int idx) {
+    if (S == 1) return (int)((w[idx >> 2] >> ((idx & 3) * 8)) & 0xffu);
+    return (int)((w[idx >> 1] >> ((idx & 1) * 16)) & 0xffffu);
+}
+
+// four pixels at columns a0..a0+3 of image row `row` -> NC component quads (shifted, transformed)
+template <int NC, int NCH, int S, bool FAST>
+__device__ __forceinline__ void load_px(const DwtPxJob& j, const DwtPxSrc& ps, int row, int a0, unsigned gm, Q<int, 4>* out) {
+    constexpr int NW = NCH * S;                         // 32-bit words of four pixels
+    uint32_t w[NW];
+#pragma unroll
+    for (int k = 0; k < NW; ++k) w[k] = 0;
+    const uint8_t* rp = ps.px + (long long)row * ps.rowbytes;
+    if (gm) {
+        if (FAST || (a0 >= j.x0 && a0 + 3 < j.x1 && ((reinterpret_cast<uintptr_t>(rp + (long long)a0 * NCH * S)) & (NW % 4 == 0 ? 15 : (NW % 2 == 0 ? 7 : 3))) == 0)) {
+            const uint8_t* p = rp + (long long)a0 * NCH * S;
+            if (NW % 4 == 0) {
+#pragma unroll
+                for (int k = 0; k < NW / 4; ++k) { const uint4 t = __ldg(reinterpret_cast<const uint4*>(p) + k); w[4 * k] = t.x; w[4 * k + 1] = t.y; w[4 * k + 2] = t.z; w[4 * k + 3] = t.w; }
+            } else if (NW % 2 == 0) {
+#pragma unroll
+                for (int k = 0; k < NW / 2; ++k) { const uint2 t = __ldg(reinterpret_cast<const uint2*>(p) + k); w[2 * k] = t.x; w[2 * k + 1] = t.y; }
+            } else {
+#pragma unroll
+                for (int k = 0; k < NW; ++k) w[k] = __ldg(reinterpret_cast<const uint32_t*>(p) + k);
+            }
+        } else {
+            // region edge: reflected columns, sample by sample
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int col = mirror(a0 + k, j.x0, j.x1);
+                const uint8_t* p = rp + (long long)col * NCH * S;
+#pragma unroll
+                for (int c = 0; c < NCH; ++c) {
+                    const uint32_t v = S == 1 ? (uint32_t)__ldg(p + c) : (uint32_t)__ldg(reinterpret_cast<const uint16_t*>(p) + c);
+                    const int idx = k * NCH + c;
+                    if (S == 1) w[idx >> 2] |= v << ((idx & 3) * 8); else w[idx >> 1] |= v << ((idx & 1) * 16);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        int v[4];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            int s = px_sample<S>(w, k * NCH + 0);
+            if (NCH > 1 && ps.chan[c] == 1) s = px_sample<S>(w, k * NCH + 1);
+            if (NCH > 2 && ps.chan[c] == 2) s = px_sample<S>(w, k * NCH + 2);
+            if (NCH > 3 && ps.chan[c] == 3) s = px_sample<S>(w, k * NCH + 3);
+            s -= j.dc[c];
+            v[c] = j.irreversible ? s << 11 : s;
+        }
+        if (NC >= 3 && j.mct) {
+            const int r = v[0], g = v[1], b = v[2];
+            if (!j.irreversible) { v[0] = (r + 2 * g + b) >> 2; v[1] = b - g; v[2] = r - g; }
+            else {
+                v[0] = fm13(r, 2449) + fm13(g, 4809) + fm13(b, 934);
+                v[1] = -fm13(r, 1382) - fm13(g, 2714) + fm13(b, 4096);
+                v[2] = fm13(r, 4096) - fm13(g, 3430) - fm13(b, 666);
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < NC; ++c) out[c].v[k] = gm ? v[c] : 0;
+    }
+}
+
+template <class L, int NC, int NCH, int S, bool FAST>
+__device__ __forceinline__ void forward_rows_px(const DwtPxJob& j, const DwtPxSrc& ps, const StripCtx& c) {
+    constexpr int N = 4;
+    const Region& g = c.g;
+    const int a0 = c.a0;
+    auto ld = [&](int n, Q<int, N>* q) { load_px<NC, NCH, S, FAST>(j, ps, mirror(n, g.y0, g.y1), a0, c.gm, q); };
+    L lift[NC];
+    const int n0 = c.e_first + L::LAG - 2 * L::WARM;
+    {
+        Q<int, N> q[NC];
+        ld(n0 - 2, q);
+#pragma unroll
+        for (int k = 0; k < NC; ++k) lift[k].init(q[k]);
+    }
+    const int n_end = c.e_last + L::LAG;
+    Q<int, N> po[NC], pe[NC];                       // the next row pair, fetched one iteration ahead
+    ld(n0 - 1, po); ld(n0, pe);
+#pragma unroll 1
+    for (int n = n0; n <= n_end; n += 2) {
+        Q<int, N> xo[NC], xv[NC];
+#pragma unroll
+        for (int k = 0; k < NC; ++k) { xo[k] = po[k]; xv[k] = pe[k]; }
+        if (n + 2 <= n_end) { ld(n + 1, po); ld(n + 2, pe); }
+        const int e = n - L::LAG;
+        const int mlo = (e >> 1) - ((g.y0 + 1) >> 1), mhi = g.sny + ((e + 1) >> 1) - (g.y0 >> 1);
+#pragma unroll
+        for (int k = 0; k < NC; ++k) {
+            Q<int, N> lo, hi;
+            lift[k].step(xo[k], xv[k], lo, hi);
+            if (e < c.e_first) continue;                      // warm-up (warp-uniform)
+            if (FAST || c.wide) { L::horizontal(lo); L::horizontal(hi); }
+            else {
+                const int oddx = g.x0 & 1;
+                lo.v[oddx] = L::single(lo.v[oddx], oddx); hi.v[oddx] = L::single(hi.v[oddx], oddx);
+            }
+            if (!c.owner) continue;
+            int* dst = j.dst[k];
+            if (FAST) {
+                int* dcol = dst + ((a0 >> 1) - ((g.x0 + 1) >> 1));
+                if (e >= g.y0 && e < g.y1) store_split_fast<int, N>(dcol + (size_t)mlo * g.pitch, g.snx, lo);
+                if (e + 1 >= g.y0 && e + 1 < g.y1) store_split_fast<int, N>(dcol + (size_t)mhi * g.pitch, g.snx, hi);
+            } else {
+                if (e >= g.y0 && e < g.y1) store_split<int, N>(dst, g, mlo, a0, lo);
+                if (e + 1 >= g.y0 && e + 1 < g.y1) store_split<int, N>(dst, g, mhi, a0, hi);
+            }
+        }
+    }
+}
+
+template <class L, int NC, int NCH, int S>
+__global__ void __launch_bounds__(32 * WARPS_PER_CTA)
+k_dwt_forward_px(const DwtPxJob* __restrict__ jobs, const DwtPxSrc ps) {
+    constexpr int N = 4;
+    const DwtPxJob job = jobs[blockIdx.y];
+    const int lane = threadIdx.x & 31;
+    const int item = blockIdx.x * WARPS_PER_CTA + (threadIdx.x >> 5);
+    if (item >= job.nstrips * job.nsegs) return;
+    const int strip = item % job.nstrips, seg = item / job.nstrips;
+    StripCtx c;
+    Region& g = c.g;
+    g.x0 = job.x0; g.y0 = job.y0; g.x1 = job.x1; g.y1 = job.y1; g.pitch = job.pitch;
+    g.snx = ((g.x1 + 1) >> 1) - ((g.x0 + 1) >> 1);
+    g.sny = ((g.y1 + 1) >> 1) - ((g.y0 + 1) >> 1);
+    const int xe = g.x0 & ~1, ye = g.y0 & ~1;
+    c.owners = job.strip_cols / N;
+    const int s0 = xe + strip * job.strip_cols;
+    c.a0 = s0 - N + lane * N;
+    c.owner = lane >= 1 && lane <= c.owners;
+    c.gm = group_mask<N>(g, c.a0, lane, c.owners);
+    c.wide = (g.x1 - g.x0) > 1;
+    c.vec_ok = false;
+    c.e_first = ye + 2 * seg * job.strip0;
+    c.e_last = c.e_first + 2 * (job.strip0 - 1);
+    if (c.e_last > g.y1 - 1) c.e_last = (g.y1 - 1) & ~1;
+    // interior strip, everything aligned: branch-free loads and stores
+    constexpr int NW = NCH * S;
+    constexpr int LA = NW % 4 == 0 ? 15 : (NW % 2 == 0 ? 7 : 3);
+    bool fast = ((g.x0 & 1) == 0) && ((g.pitch & 3) == 0) && s0 - 4 >= g.x0 && s0 + c.owners * N + 4 <= g.x1 && ((s0 - g.x0) & 3) == 0 &&
+                ((g.x0 >> 1) & 1) == 0 && (g.snx & 1) == 0 && ((reinterpret_cast<uintptr_t>(ps.px) | (uintptr_t)ps.rowbytes) & LA) == 0 &&
+                (((long long)s0 * NCH * S) & LA) == 0;
+#pragma unroll
+    for (int k = 0; k < NC; ++k) fast = fast && ((reinterpret_cast<uintptr_t>(job.dst[k]) & 15) == 0);
+    if (fast) forward_rows_px<L, NC, NCH, S, true>(job, ps, c);
+    else forward_rows_px<L, NC, NCH, S, false>(job, ps, c);
+}
+
 // ---- lifting kernels (inverse) -----------------------------------------------------------------
 // Vertical streaming step: new low row a = L(n), new high row b = H(n+1); emits the finished pair
 // (row n-LAG, row n-LAG+1).
@@ -751,6 +912,25 @@ void launch_dwt_forward(const DwtJob* d_jobs, int njobs, int max_items, int /*se
     dim3 grid((max_items + WARPS_PER_CTA - 1) / WARPS_PER_CTA, njobs), block(32 * WARPS_PER_CTA);
     if (kind == DWT_53) launch_fwd<Fwd53>(grid, block, st, d_jobs);
     else launch_fwd<Fwd97>(grid, block, st, d_jobs);
+}
+
+// Measured on B200 (4K RGBA16, profiles/README.md): the fused kernel needs 164 registers (12 warps per SM) and takes 122 us where
+// k_mct_forward + level 1 take 46 + 60 us, so it is opt-in (J2KCUDA_FUSE_L1=1) until it beats them.
+bool dwt_px_fusion_available() { const char* e = getenv("J2KCUDA_FUSE_L1"); return tune().ncol == 4 && e && e[0] == '1'; }
+
+template <template <int> class L>
+static bool launch_fwd_px(dim3 grid, dim3 block, cudaStream_t st, const DwtPxJob* j, const DwtPxSrc& ps, int nc, int nch, int S) {
+#define J2K_PX(NC_, NCH_, S_) if (nc == NC_ && nch == NCH_ && S == S_) { k_dwt_forward_px<L<4>, NC_, NCH_, S_><<<grid, block, 0, st>>>(j, ps); return true; }
+    J2K_PX(3, 3, 1) J2K_PX(3, 3, 2) J2K_PX(4, 4, 1) J2K_PX(4, 4, 2) J2K_PX(3, 4, 1) J2K_PX(3, 4, 2)
+#undef J2K_PX
+    return false;
+}
+bool launch_dwt_forward_px(const DwtPxJob* d_jobs, const DwtPxSrc& src, int njobs, int max_items, int kind, int ncomp, int nch, int sample_bytes,
+                           cudaStream_t st) {
+    if (njobs <= 0 || max_items <= 0) return false;
+    dim3 grid((max_items + WARPS_PER_CTA - 1) / WARPS_PER_CTA, njobs), block(32 * WARPS_PER_CTA);
+    return kind == DWT_53 ? launch_fwd_px<Fwd53>(grid, block, st, d_jobs, src, ncomp, nch, sample_bytes)
+                          : launch_fwd_px<Fwd97>(grid, block, st, d_jobs, src, ncomp, nch, sample_bytes);
 }
 
 void launch_dwt_inverse(const DwtJob* d_jobs, int njobs, int max_items, int /*seg_pairs*/, int kind, cudaStream_t st) {

@@ -51,6 +51,7 @@ struct j2kcuda_encoder {
     std::vector<std::vector<DwtJob>> level_jobs;     // [level-1]
     std::vector<int> level_items, level_seg;
     DwtJob* d_jobs = nullptr;                        // all levels, concatenated
+    DwtPxJob* d_px_jobs = nullptr; int n_px_jobs = 0, px_items = 0;   // level 1 fused with unpack + shift + RCT/ICT (one job per tile)
     std::vector<int> level_off;
     // tier-1
     int nblocks = 0;
@@ -83,7 +84,7 @@ static void free_encoder(j2kcuda_encoder* e) {
     cudaSetDevice(e->device);
     for (int c = 0; c < 4; ++c) { cudaFree(e->planeA[c]); cudaFree(e->planeB[c]); }
     cudaFree(e->d_pix); cudaFreeHost(e->h_pix);
-    cudaFree(e->d_mq_order); cudaFree(e->d_jobs); cudaFree(e->d_blocks); cudaFree(e->d_sym); cudaFree(e->d_out);
+    cudaFree(e->d_mq_order); cudaFree(e->d_jobs); cudaFree(e->d_px_jobs); cudaFree(e->d_blocks); cudaFree(e->d_sym); cudaFree(e->d_out);
     cudaFree(e->d_pass_nsym); cudaFree(e->d_results); cudaFree(e->d_offsets); cudaFree(e->d_packed);
     cudaFreeHost(e->h_results); cudaFreeHost(e->h_offsets); cudaFreeHost(e->h_packed);
     for (auto& ev : e->ev) if (ev) cudaEventDestroy(ev);
@@ -197,6 +198,31 @@ static int setup_encoder(j2kcuda_encoder* e) {
     if (!all.empty()) {
         CK(cudaMalloc(&e->d_jobs, all.size() * sizeof(DwtJob)));
         CK(cudaMemcpy(e->d_jobs, all.data(), all.size() * sizeof(DwtJob), cudaMemcpyHostToDevice));
+    }
+    // level 1 fused with the sample unpacking and the component transform: one job per tile over all components
+    if (levels >= 1 && e->ncomp >= 3 && dwt_px_fusion_available() && !e->level_jobs[0].empty() && e->level_jobs[0].size() % (size_t)e->ncomp == 0) {
+        const auto& v = e->level_jobs[0];                    // tile-major, then component
+        std::vector<DwtPxJob> pj;
+        bool ok = true;
+        for (size_t i = 0; i < v.size() && ok; i += (size_t)e->ncomp) {
+            DwtPxJob j;
+            memset(&j, 0, sizeof(j));
+            for (int c = 0; c < e->ncomp; ++c) {
+                const DwtJob& d = v[i + (size_t)c];
+                ok = ok && d.x0 == v[i].x0 && d.y0 == v[i].y0 && d.x1 == v[i].x1 && d.y1 == v[i].y1 && d.y1 - d.y0 >= 2;
+                j.dst[c] = d.dst;
+                j.dc[c] = cp.comps[c].sgnd ? 0 : 1 << (cp.comps[c].prec - 1);
+            }
+            j.x0 = v[i].x0; j.y0 = v[i].y0; j.x1 = v[i].x1; j.y1 = v[i].y1; j.pitch = v[i].pitch;
+            j.strip0 = v[i].strip0; j.nstrips = v[i].nstrips; j.nsegs = v[i].nsegs; j.strip_cols = v[i].strip_cols;
+            j.mct = cp.mct ? 1 : 0; j.irreversible = e->irreversible;
+            pj.push_back(j);
+        }
+        if (ok) {
+            CK(cudaMalloc(&e->d_px_jobs, pj.size() * sizeof(DwtPxJob)));
+            CK(cudaMemcpy(e->d_px_jobs, pj.data(), pj.size() * sizeof(DwtPxJob), cudaMemcpyHostToDevice));
+            e->n_px_jobs = (int)pj.size(); e->px_items = e->level_items[0];
+        }
     }
     if (e->nblocks) {
         CK(cudaMalloc(&e->d_blocks, e->nblocks * sizeof(T1Block)));
@@ -442,7 +468,25 @@ int j2kcuda_encoder_run(j2kcuda_encoder* e) { return j2k::guarded([&]() -> int {
     cudaStream_t st = e->st;
     uint64_t launches = 0;
     CK(cudaEventRecord(e->ev[0], st));
-    {
+    // Fused first level: straight from the caller's interleaved pixels when they need no depth / sign conversion
+    bool fused = false;
+    if (e->n_px_jobs && (e->src.sample_bytes == 1 || e->src.sample_bytes == 2)) {
+        DwtPxSrc ps;
+        memset(&ps, 0, sizeof(ps));
+        const int nch = detect_pixel_interleave(e->src, e->ncomp, ps.chan);
+        bool plain = nch == 3 || nch == 4;
+        for (int c = 0; c < e->ncomp && plain; ++c) plain = e->mp.conv[c].plain != 0;
+        if (plain) {
+            const uint8_t* lo = e->src.base[0];
+            for (int c = 1; c < e->ncomp; ++c) if (e->src.base[c] < lo) lo = e->src.base[c];
+            ps.px = lo; ps.rowbytes = e->src.rowbytes[0];
+            CK(cudaEventRecord(e->ev[1], st));
+            fused = launch_dwt_forward_px(e->d_px_jobs, ps, e->n_px_jobs, e->px_items, e->irreversible ? DWT_97_FIX : DWT_53, e->ncomp, nch,
+                                          e->src.sample_bytes, st);
+            if (fused) ++launches;
+        }
+    }
+    if (!fused) {
         // only the image rows this context's tiles cover (all of them unless a tile range is set)
         PixelSrc src = e->src;
         MctParams mp = e->mp;
@@ -454,11 +498,12 @@ int j2kcuda_encoder_run(j2kcuda_encoder* e) { return j2k::guarded([&]() -> int {
         mp.height = e->row1 - e->row0;
         if (mp.height > 0) { launch_mct_forward(src, mp, planes, st); ++launches; }
     }
-    CK(cudaEventRecord(e->ev[1], st));
+    if (!fused) CK(cudaEventRecord(e->ev[1], st));
     const int levels = e->numres - 1;
     for (int l = 0; l < levels; ++l) {
         if (e->level_jobs[l].empty()) continue;
         if (l == 1) CK(cudaEventRecord(e->ev[6], st));
+        if (l == 0 && fused) continue;
         launch_dwt_forward(e->d_jobs + e->level_off[l], (int)e->level_jobs[l].size(), e->level_items[l], e->level_seg[l],
                            e->irreversible ? DWT_97_FIX : DWT_53, st);
         ++launches;

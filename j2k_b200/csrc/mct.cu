@@ -308,6 +308,8 @@ int grid_for(long long threads) {
         else KERNEL<4, 0><<<GRID, 256, 0, ST>>>(ARGS);                                            \
     } while (0)
 
+int detect_pixel_interleave(const PixelSrc& s, int ncomp, int chan[4]) { return detect_interleave(s, ncomp, chan); }
+
 void launch_mct_forward(const PixelSrc& src, const MctParams& mp, int32_t* const planes[4], cudaStream_t st) {
     FwdArgs a;
     a.src = src; a.mp = mp;

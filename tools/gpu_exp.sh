@@ -28,4 +28,8 @@ dwtsweep)  # per-level tunables of the DWT kernels (J2KCUDA_DWT_*), forward and 
     env $cfg python tools/stage_times.py decode1 2>&1 | grep -E "idwt" >> gpurun_out/dwtsweep.log
   done
   cat gpurun_out/dwtsweep.log ;;
+bench)     # bench.py on this box: tools/gpu_exp.sh bench <name> [bench.py args...]
+  name=${2:-bench}; shift 2
+  python bench.py "$@" > gpurun_out/$name.json 2> gpurun_out/$name.err; tail -2 gpurun_out/$name.err
+  python tools/bench_summary.py gpurun_out/$name.json ;;
 esac
