@@ -74,6 +74,9 @@ if __name__ == "__main__":
         for kind in ("smooth", "noise"):
             run(2160, 4096, 3, 12, kind, reps=4, irreversible=1, mct=1, profile=L.PROFILE_CINEMA_4K)
             run_decode(2160, 4096, 3, 12, kind, irreversible=1, mct=1, profile=L.PROFILE_CINEMA_4K)
+    elif "roundtrip1" in sys.argv:       # the ncu --set full target: every kernel of one 4K RGBA16 encode + decode (one warm pass first)
+        run(2160, 4096, 4, 16, "smooth", reps=2, mct=1)
+        run_decode(2160, 4096, 4, 16, "smooth", reps=2, mct=1)
     elif "dwt" in sys.argv:
         run(2160, 4096, 4, 16, "smooth", reps=6, mct=1)
     elif "decode1" in sys.argv:
