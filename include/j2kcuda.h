@@ -297,6 +297,27 @@ int j2kcuda_stage_t1_encode(const int32_t* plane, int stride, int height, const 
  * (t1.cpp:1337-1448: magnitude with one extra fractional bit). */
 int j2kcuda_stage_t1_decode(const uint8_t* data, const int32_t* blk, int nblk, int32_t* out);
 
+/* ---- allocation-free forward DWT on DEVICE planes -------------------------------------------
+ * No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same transform as j2kcuda_stage_dwt(..., inverse = 0) -- 5/3, or the 9/7 in the
+ * reference's Q13 fixed point when `irreversible` -- but input and output are the CALLER'S device
+ * planes (int32, `pitch` samples per row, pitch >= x1 - x0 and a multiple of 4, both 16-byte
+ * aligned, not aliased; the input is not modified) and the ping-pong plane + job table every
+ * other path allocates live in one file-scope device array of fixed size inside the library
+ * (dwt.cu; J2KCUDA_NOALLOC_MAX_SCRATCH_SAMPLES * 4 + 4096 bytes, held by every GPU that loads the
+ * library until the process exits).  The call makes no cudaMalloc / cudaFree / allocating library
+ * call, enqueues its kernels and device-to-device copies on `stream` (a cudaStream_t, NULL = the
+ * default stream) of the CURRENT device and returns without synchronising.
+ * Limit: pitch * ceil((y1 - y0) / 2) <= J2KCUDA_NOALLOC_MAX_SCRATCH_SAMPLES when numres >= 3
+ * (e.g. 2048 x 2048 or 4096 x 1024), else J2KCUDA_ERR_UNSUPPORTED with the sizes in the message.
+ * All calls on one device share the scratch array, which keeps the previous call's contents
+ * (nothing in it has to start at zero: each level reads only what the level before wrote): calls
+ * whose work overlaps on the GPU race -- order them on one stream or with events. */
+#define J2KCUDA_NOALLOC_MAX_SCRATCH_SAMPLES (2u * 1024u * 1024u)       /* 8 MiB of int32 */
+int j2kcuda_dwt_forward_noalloc(const int32_t* d_in, int32_t* d_out, int pitch, int x0, int y0,
+                                int x1, int y1, int numres, int irreversible, void* stream);
+
 /* Host Tier-2 alone, from externally supplied code-block results (the grok plug-in hand-off,
  * plugin_bridge.cpp:72-174): blocks in tile -> component -> resolution -> band -> precinct ->
  * code-block order.  rates are raw cumulative `mqc_numbytes + 3` values already clamped and

@@ -941,3 +941,128 @@ void launch_dwt_inverse(const DwtJob* d_jobs, int njobs, int max_items, int /*se
 }
 
 }  // namespace j2k
+
+// ---- j2kcuda_dwt_forward_noalloc: the forward transform for callers that cannot allocate -----------------------------
+// No counterpart in the reference (include/j2kcuda.h).  The multi-level
+// forward transform needs a second plane to ping-pong with and a table of per-level job descriptors
+// in device memory.  The existing paths cudaMalloc both; this one keeps them in a file-scope device array of fixed size,
+// which every GPU that loads libj2kcuda.so holds until the process ends.
+//
+//   level 1:            caller's input  -> caller's output (all four bands of level 1 at their Mallat position)
+//   level 2, 4, ...:    output's LL     -> scratch plane   (same pitch as the output, only the rows of LL1 exist)
+//   level 3, 5, ...:    scratch's LL    -> output
+//   afterwards the detail bands of the even levels (and the last LL when the level count is even) are copied from the
+//   scratch plane to their place in the output (device-to-device 2D copies on the same stream).
+//
+// Nothing in the scratch has to start at zero: every sample a level reads was written by the level before it in the same
+// call.  Every call on a device uses the same array: two calls whose work overlaps on the GPU (different streams without
+// an event between them, or different host threads) race on it.
+#include "../../include/j2kcuda.h"
+#include "common.h"
+#include "geometry.h"
+#include <mutex>
+
+namespace {
+
+constexpr size_t kNoAllocHeaderBytes = 4096;                              // job table: 32 levels x sizeof(DwtJob)
+constexpr size_t kNoAllocPlaneSamples = (size_t)J2KCUDA_NOALLOC_MAX_SCRATCH_SAMPLES;
+static_assert(32 * sizeof(j2k::DwtJob) <= kNoAllocHeaderBytes, "job table does not fit the scratch header");
+
+static __device__ __align__(256) unsigned char g_dwt_noalloc_scratch[kNoAllocHeaderBytes + kNoAllocPlaneSamples * 4];
+
+struct NoAllocJobs { j2k::DwtJob job[32]; int n; };
+
+// Device code may name the array directly: the job table goes in by value (a kernel parameter, no host-to-device copy)
+__global__ void k_dwt_noalloc_jobs(NoAllocJobs t) {
+    j2k::DwtJob* dst = reinterpret_cast<j2k::DwtJob*>(g_dwt_noalloc_scratch);
+    for (int i = threadIdx.x; i < t.n; i += blockDim.x) dst[i] = t.job[i];
+}
+
+// Host code needs the array's DEVICE address (the symbol's name is only a host-side stand-in): asked for once per device,
+// with that device current.
+std::mutex g_noalloc_mu;
+unsigned char* g_noalloc_ptr[64] = {};
+
+int noalloc_scratch(unsigned char** out) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+        cudaGetLastError();
+        return j2k::set_error(J2KCUDA_ERR_NO_DEVICE, "no CUDA device: libj2kcuda has no CPU path");
+    }
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_dwt_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            cudaGetLastError();
+            return j2k::set_error(J2KCUDA_ERR_CUDA, std::string("cudaGetSymbolAddress(scratch): ") + cudaGetErrorString(e));
+        }
+        g_noalloc_ptr[dev] = static_cast<unsigned char*>(p);
+    }
+    *out = g_noalloc_ptr[dev];
+    return J2KCUDA_OK;
+}
+
+}  // namespace
+
+extern "C" int j2kcuda_dwt_forward_noalloc(const int32_t* d_in, int32_t* d_out, int pitch, int x0, int y0, int x1, int y1,
+                                           int numres, int irreversible, void* stream) { return j2k::guarded([&]() -> int {
+    using namespace j2k;
+    if (!d_in || !d_out || d_in == d_out) return set_error(J2KCUDA_ERR_PARAM, "j2kcuda_dwt_forward_noalloc: null or aliased plane");
+    if (x0 < 0 || y0 < 0 || x1 <= x0 || y1 <= y0 || numres < 1 || numres > 33) return set_error(J2KCUDA_ERR_PARAM, "j2kcuda_dwt_forward_noalloc: bad region");
+    const int w = x1 - x0, h = y1 - y0, levels = numres - 1;
+    if (pitch < w || (pitch & 3) || (((uintptr_t)d_in | (uintptr_t)d_out) & 15))
+        return set_error(J2KCUDA_ERR_PARAM, "j2kcuda_dwt_forward_noalloc: pitch must be >= width and a multiple of 4 samples, planes 16-byte aligned");
+    // rows of the level-1 LL band = rows the scratch plane needs (it has the output's pitch)
+    const int ll_rows = (int)ceildivpow2((uint32_t)y1, 1) - (int)ceildivpow2((uint32_t)y0, 1);
+    if (levels >= 2 && (size_t)pitch * (size_t)ll_rows > kNoAllocPlaneSamples)
+        return set_error(J2KCUDA_ERR_UNSUPPORTED, "j2kcuda_dwt_forward_noalloc: pitch * ceil(height / 2) = " + std::to_string((size_t)pitch * (size_t)ll_rows) +
+                         " samples exceeds the fixed scratch of J2KCUDA_NOALLOC_MAX_SCRATCH_SAMPLES = " + std::to_string(kNoAllocPlaneSamples) +
+                         "; use j2kcuda_stage_dwt or an encoder context for larger planes");
+    unsigned char* base = nullptr;
+    if (int rc = noalloc_scratch(&base)) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    DwtJob* d_jobs = reinterpret_cast<DwtJob*>(base);
+    int32_t* scratch = reinterpret_cast<int32_t*>(base + kNoAllocHeaderBytes);
+    const int kind = irreversible ? DWT_97_FIX : DWT_53;
+
+    if (levels == 0) {                                   // nothing to transform: the output is the input
+        if (cudaMemcpy2DAsync(d_out, (size_t)pitch * 4, d_in, (size_t)pitch * 4, (size_t)w * 4, (size_t)h, cudaMemcpyDeviceToDevice, st) != cudaSuccess)
+            return set_error(J2KCUDA_ERR_CUDA, cudaGetErrorString(cudaGetLastError()));
+        return J2KCUDA_OK;
+    }
+    // plane(0) = input, odd levels land in the output, even levels in the scratch
+    auto plane = [&](int l) -> int32_t* { return l == 0 ? const_cast<int32_t*>(d_in) : (l & 1) ? d_out : scratch; };
+    NoAllocJobs tab{};
+    int items[32], done = 0;
+    for (int l = 1; l <= levels && l <= 32; ++l) {
+        DwtJob& j = tab.job[tab.n];
+        j.x0 = (int)ceildivpow2((uint32_t)x0, l - 1); j.x1 = (int)ceildivpow2((uint32_t)x1, l - 1);
+        j.y0 = (int)ceildivpow2((uint32_t)y0, l - 1); j.y1 = (int)ceildivpow2((uint32_t)y1, l - 1);
+        j.pitch = pitch; j.strip0 = j.nstrips = j.nsegs = 0; j.strip_cols = 0; j.pad = 0;
+        if (j.x1 <= j.x0 || j.y1 <= j.y0) break;         // every deeper level is empty as well
+        j.src = plane(l - 1); j.dst = plane(l);
+        items[tab.n] = dwt_plan_jobs(&j, 1);
+        ++tab.n; done = l;
+    }
+    k_dwt_noalloc_jobs<<<1, 32, 0, st>>>(tab);
+    for (int i = 0; i < tab.n; ++i) launch_dwt_forward(d_jobs + i, 1, items[i], tab.job[i].strip0, kind, st);
+    if (cudaError_t e = cudaGetLastError()) return set_error(J2KCUDA_ERR_CUDA, std::string("j2kcuda_dwt_forward_noalloc: ") + cudaGetErrorString(e));
+    // even levels: their detail bands (and the final LL when the deepest level is even) move from the scratch to the output
+    for (int l = 2; l <= done; l += 2) {
+        const DwtJob& j = tab.job[l - 1];
+        const int rw = j.x1 - j.x0, rh = j.y1 - j.y0;
+        const int snx = (int)ceildivpow2((uint32_t)j.x1, 1) - (int)ceildivpow2((uint32_t)j.x0, 1);
+        const int sny = (int)ceildivpow2((uint32_t)j.y1, 1) - (int)ceildivpow2((uint32_t)j.y0, 1);
+        cudaError_t e = cudaSuccess;
+        if (l == done) {
+            e = cudaMemcpy2DAsync(d_out, (size_t)pitch * 4, scratch, (size_t)pitch * 4, (size_t)rw * 4, (size_t)rh, cudaMemcpyDeviceToDevice, st);
+        } else {
+            if (rw > snx) e = cudaMemcpy2DAsync(d_out + snx, (size_t)pitch * 4, scratch + snx, (size_t)pitch * 4, (size_t)(rw - snx) * 4, (size_t)rh, cudaMemcpyDeviceToDevice, st);
+            if (e == cudaSuccess && rh > sny && snx > 0)
+                e = cudaMemcpy2DAsync(d_out + (size_t)sny * pitch, (size_t)pitch * 4, scratch + (size_t)sny * pitch, (size_t)pitch * 4, (size_t)snx * 4, (size_t)(rh - sny), cudaMemcpyDeviceToDevice, st);
+        }
+        if (e != cudaSuccess) { cudaGetLastError(); return set_error(J2KCUDA_ERR_CUDA, std::string("j2kcuda_dwt_forward_noalloc: ") + cudaGetErrorString(e)); }
+    }
+    return J2KCUDA_OK;
+}); }
