@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--workers", type=int, default=8)
     ap.add_argument("--only", default="")
     ap.add_argument("--frames8k", type=int, default=4)
+    ap.add_argument("--devices", type=int, default=0, help="C4api / C5api: GPUs driven from ONE process through the C ABI (0 = all visible)")
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -176,7 +177,79 @@ def main():
                 "rank0_last_frame_ms": {"upload_run": phases[0] * 1e3, "host_tier2": phases[1] * 1e3, "gather": phases[2] * 1e3, "join": phases[3] * 1e3},
                 "sharding": "tiles of each frame over ranks (contiguous ranges), fragments gathered to rank 0 and joined while the next frame is encoded"}
 
+    def run_tiles_api(name, h, w, nc, prec, tile, nframes):
+        """C4 through j2kcuda_tiles_* (api_multi.cpp): ONE process, tiles of each frame over `--devices` GPUs, encode AND decode"""
+        ndev = args.devices or torch.cuda.device_count()
+        frames = [make_frame(h, w, nc, prec, args.kind, seed=100 + f) for f in range(nframes)]
+        src = pinned(frames)
+        dst = pinned([np.zeros_like(f) for f in frames])
+        p = L.default_params(width=w, height=h, ncomp=nc, prec=prec, mct=1, tile_w=tile, tile_h=tile)
+        devs = (C.c_int * ndev)(*range(ndev))
+        lib.j2kcuda_tiles_create.restype = C.c_void_p
+        t = C.c_void_p(lib.j2kcuda_tiles_create(C.byref(p), devs, ndev))
+        assert t.value, L.last_error()
+        te = td = 0.0
+        nbytes = 0
+        for rep in range(args.reps + 1):
+            outs = []
+            t0 = time.perf_counter()
+            for f in src:
+                out = C.POINTER(C.c_uint8)(); n = C.c_size_t(0)
+                assert lib.j2kcuda_tiles_encode(t, j2k.planes_of(f.numpy()), nc, C.byref(out), C.byref(n)) == 0, L.last_error()
+                outs.append((out, n.value))
+            t1 = time.perf_counter()
+            for (out, n), g in zip(outs, dst):
+                assert lib.j2kcuda_tiles_decode(t, out, C.c_size_t(n), 0, j2k.planes_of(g.numpy()), nc) == 0, L.last_error()
+            t2 = time.perf_counter()
+            if rep:
+                te += t1 - t0; td += t2 - t1
+            nbytes = outs[0][1]
+            for out, n in outs:
+                lib.j2kcuda_free(out)
+        lib.j2kcuda_tiles_destroy(t)
+        ok = all(bool((a == b).all()) for a, b in zip(src, dst))
+        mp = args.reps * nframes * w * h / 1e6
+        return {"config": name, "n_gpus": ndev, "frames_per_step": nframes, "encode_mpix_s": mp / te, "decode_mpix_s": mp / td,
+                "roundtrip_mpix_s": mp / (te + td), "codestream_bytes_per_frame": nbytes, "verified": ok,
+                "sharding": "one process, j2kcuda_tiles_*: contiguous tile runs per device, one host thread per device, joined on the host"}
+
+    def run_sequence_api(name, h, w, nc, prec, nframes, **kw):
+        """C5 through j2kcuda_sequence_create_multi: ONE process, frames over `--devices` GPUs"""
+        ndev = args.devices or torch.cuda.device_count()
+        dt = np.uint8 if prec <= 8 else np.uint16
+        F = nframes * ndev
+        src = pinned([make_frame(h, w, nc, prec, args.kind, seed=f).astype(dt) for f in range(F)])
+        dst = pinned([np.zeros((h, w, nc), dt) for _ in range(F)])
+        p = L.default_params(width=w, height=h, ncomp=nc, prec=prec, **kw)
+        devs = (C.c_int * ndev)(*range(ndev))
+        lib.j2kcuda_sequence_create_multi.restype = C.c_void_p
+        cores = os.cpu_count() or 8
+        wpd = max(4, min(args.workers, cores // ndev))
+        seq = C.c_void_p(lib.j2kcuda_sequence_create_multi(C.byref(p), devs, ndev, wpd))
+        assert seq.value, L.last_error()
+        tin, k1 = table(src); tout, k2 = table(dst)
+        outs = (C.POINTER(C.c_uint8) * F)(); lens = (C.c_size_t * F)()
+        te = td = 0.0
+        for rep in range(args.reps + 1):
+            t0 = time.perf_counter()
+            assert lib.j2kcuda_sequence_encode(seq, tin, F, nc, 0, outs, lens) == 0, L.last_error()
+            t1 = time.perf_counter()
+            assert lib.j2kcuda_sequence_decode(seq, C.cast(outs, C.POINTER(C.POINTER(C.c_uint8))), lens, F, 0, tout, nc, 0) == 0, L.last_error()
+            t2 = time.perf_counter()
+            if rep:
+                te += t1 - t0; td += t2 - t1
+            for i in range(F):
+                lib.j2kcuda_free(outs[i])
+        lib.j2kcuda_sequence_destroy(seq)
+        ok = all(bool((a == b).all()) for a, b in zip(src, dst))
+        mp = args.reps * F * w * h / 1e6
+        return {"config": name, "n_gpus": ndev, "frames_per_step": F, "workers_per_device": wpd, "encode_mpix_s": mp / te, "decode_mpix_s": mp / td,
+                "roundtrip_mpix_s": mp / (te + td), "verified": ok,
+                "sharding": "one process, j2kcuda_sequence_create_multi: frames to whichever device has a free worker"}
+
     jobs = [
+        ("C4api", lambda: run_tiles_api("C4 8192x4320 16-bit RGB lossless, 1024x1024 tiles, j2kcuda_tiles_* in one process", 4320, 8192, 3, 16, 1024, args.frames8k)),
+        ("C5api", lambda: run_sequence_api("C5 4096x2160 16-bit RGB lossless sequence, j2kcuda_sequence_create_multi in one process", 2160, 4096, 3, 16, 16, mct=1)),
         ("C1", lambda: run_sequence("C1 2048x1080 8-bit RGB lossless 5/3", 1080, 2048, 3, 8, 16, True, mct=1)),
         ("C2", lambda: run_sequence("C2 4096x2160 16-bit RGBA lossless 5/3", 2160, 4096, 4, 16, 8, True, mct=1)),
         ("C3", lambda: run_sequence("C3 DCI 4K 12-bit XYZ 9/7 ICT cinema profile (PCRD rate cap)", 2160, 4096, 3, 12, 8, False,
@@ -185,7 +258,7 @@ def main():
         ("C5", lambda: run_sequence("C5 4096x2160 16-bit RGB lossless sequence", 2160, 4096, 3, 16, 16, True, mct=1)),
     ]
     for key, fn in jobs:
-        if args.only and key not in args.only.split(","):
+        if (args.only and key not in args.only.split(",")) or (not args.only and key.endswith("api")) or (key.endswith("api") and world > 1):
             continue
         r = fn()
         if rank == 0:
