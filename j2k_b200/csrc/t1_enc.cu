@@ -19,6 +19,7 @@
 // top to bottom inside a column.
 #include "device.h"
 #include "t1_tables.cuh"
+#include <cstdlib>
 
 namespace j2k {
 namespace {
@@ -57,6 +58,11 @@ __device__ __forceinline__ int nmsedec_ref(const Luts& L, uint32_t mag, int bpno
 
 // Byte-stream writer of one lane: symbols go out as aligned 32-bit words where the lane owns the
 // whole word, as single bytes at the ragged ends it shares with its neighbours.
+// bytes [from, to) of the word being assembled, one at a time: the ragged first / last word of a lane's piece.  Out of line on
+// purpose: inlined at every push it was 40 % of the kernel's code, which then no longer fitted the instruction cache.
+__device__ __noinline__ void store_ragged(uint8_t* base, uint32_t from, uint32_t to, uint32_t acc) {
+    for (uint32_t p = from; p < to; ++p) base[p] = (uint8_t)(acc >> ((p & 3) * 8));
+}
 struct Emitter {
     uint8_t* base;
     uint32_t first, pos, acc;
@@ -66,15 +72,15 @@ struct Emitter {
         ++pos;
         if ((pos & 3) == 0) flush_word();
     }
-    __device__ void flush_word() {
-        uint32_t w0 = pos - 4;
+    __device__ __forceinline__ void flush_word() {
+        const uint32_t w0 = pos - 4;
         if (w0 >= first) *reinterpret_cast<uint32_t*>(base + w0) = acc;
-        else for (uint32_t p = first; p < pos; ++p) base[p] = (uint8_t)(acc >> ((p & 3) * 8));
+        else store_ragged(base, first, pos, acc);
         acc = 0;
     }
-    __device__ void finish() {
-        uint32_t w0 = pos & ~3u;
-        for (uint32_t p = (w0 > first ? w0 : first); p < pos; ++p) base[p] = (uint8_t)(acc >> ((p & 3) * 8));
+    __device__ __forceinline__ void finish() {
+        const uint32_t w0 = pos & ~3u;
+        store_ragged(base, w0 > first ? w0 : first, pos, acc);
     }
 };
 
@@ -239,7 +245,8 @@ __device__ uint32_t emit_pass(const Rows& R, const Luts& L, const T1Block& blk, 
     return total;
 }
 
-__global__ void __launch_bounds__(32 * CX_WARPS)
+template <int MINB>
+__global__ void __launch_bounds__(32 * CX_WARPS, MINB)
 k_t1_context(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __restrict__ tab,
              uint8_t* __restrict__ sym_arena, uint32_t* __restrict__ pass_nsym, T1Result* __restrict__ results) {
     __shared__ Rows s_rows[CX_WARPS];
@@ -631,7 +638,12 @@ __global__ void __launch_bounds__(256) k_t1_gather(const T1Block* __restrict__ b
 void launch_t1_context(const T1Block* d_blocks, int nblocks, uint8_t* sym_arena, uint32_t* pass_nsym,
                        T1Result* results, cudaStream_t st) {
     if (nblocks <= 0) return;
-    k_t1_context<<<(nblocks + CX_WARPS - 1) / CX_WARPS, 32 * CX_WARPS, 0, st>>>(d_blocks, nblocks, t1_tables_device(), sym_arena, pass_nsym, results);
+    // resident CTAs per SM the register allocation aims at (4: 124 registers, 5: 96, 6: 80 with a few spills); J2KCUDA_CX_MINB to compare
+    static const int minb = [] { const char* e = getenv("J2KCUDA_CX_MINB"); const int v = e ? atoi(e) : 4; return v < 4 ? 4 : v > 6 ? 6 : v; }();
+    const dim3 grid((nblocks + CX_WARPS - 1) / CX_WARPS), block(32 * CX_WARPS);
+    if (minb == 4) k_t1_context<4><<<grid, block, 0, st>>>(d_blocks, nblocks, t1_tables_device(), sym_arena, pass_nsym, results);
+    else if (minb == 5) k_t1_context<5><<<grid, block, 0, st>>>(d_blocks, nblocks, t1_tables_device(), sym_arena, pass_nsym, results);
+    else k_t1_context<6><<<grid, block, 0, st>>>(d_blocks, nblocks, t1_tables_device(), sym_arena, pass_nsym, results);
 }
 
 void launch_t1_mq(const T1Block* d_blocks, int nblocks, const uint8_t* sym_arena, const uint32_t* pass_nsym,

@@ -32,4 +32,12 @@ bench)     # bench.py on this box: tools/gpu_exp.sh bench <name> [bench.py args.
   name=${2:-bench}; shift 2
   python bench.py "$@" > gpurun_out/$name.json 2> gpurun_out/$name.err; tail -2 gpurun_out/$name.err
   python tools/bench_summary.py gpurun_out/$name.json ;;
+cxsweep)   # resident CTAs of k_t1_context (J2KCUDA_CX_MINB): per-stage times alone and the batch throughput
+  : > gpurun_out/cxsweep.log
+  for mb in 4 5 6; do
+    echo "== J2KCUDA_CX_MINB=$mb" >> gpurun_out/cxsweep.log
+    J2KCUDA_CX_MINB=$mb python tools/stage_times.py dwt 2>&1 | grep -E "t1ctx" >> gpurun_out/cxsweep.log
+    J2KCUDA_CX_MINB=$mb python bench.py --steps 3 --warmup 2 --no-cpu-baseline 2>/dev/null | python tools/bench_summary.py /dev/stdin | head -1 >> gpurun_out/cxsweep.log
+  done
+  cat gpurun_out/cxsweep.log ;;
 esac
