@@ -31,8 +31,8 @@ W, H, NC, PREC = 4096, 2160, 4, 16
 WORKLOAD = "4096x2160 16-bit RGBA lossless 5/3 (RCT, 6 resolutions, 64x64 code-blocks, 1 tile)"
 FRAMES = 16  # frames per step per GPU (one batch of the image sequence): 16 x 70.8 MB of input and 283 MB of
              # planes per frame in flight -- far beyond the 126 MB L2, so no flush is needed between steps
-TRAFFIC_L1 = 240044544  # dram__bytes_read.sum 142 349 312 + dram__bytes_write.sum 97 695 232 of one level-1 launch, from the
-                        # ncu --set full capture in profiles/r1_roundtrip_full_raw.csv (part of the 141.6 MB written stays in L2)
+TRAFFIC_L1 = 239819520  # dram__bytes_read.sum 142 357 760 + dram__bytes_write.sum 97 461 760 of one level-1 launch, from the
+                        # ncu --set full capture in profiles/r2_frame_full_raw.csv.gz (part of the 141.6 MB written stays in L2)
 WORKERS = 16  # contexts (stream + buffers + host thread) the sequence keeps in flight
 
 
@@ -422,7 +422,7 @@ def main():
                                     "forward": {"ms": float(solo_enc[2]), "achieved": all_bytes / (float(solo_enc[2]) * 1e-3) / 1e9, "frac": all_bytes / (float(solo_enc[2]) * 1e-3) / 1e9 / peak},
                                     "inverse": {"ms": float(solo_dec[3]), "achieved": all_bytes / (float(solo_dec[3]) * 1e-3) / 1e9, "frac": all_bytes / (float(solo_dec[3]) * 1e-3) / 1e9 / peak},
                                     "note": "BASELINE.md 4: 8 B per sample of every level's input region, all five launches of one frame (CUDA events around them, frame alone)"},
-                     "traffic_source": "profiles/r1_roundtrip_full_raw.csv (ncu --set full, commit 03157f7; the level-1 kernels are unchanged since)"},
+                     "traffic_source": "profiles/r2_frame_full_raw.csv.gz (ncu --set full of tools/stage_times.py roundtrip1, round 2)"},
         "value_noise": {"value": v_noise, "unit": "MPix/s", "frames_per_step_per_gpu": nf_noise,
                         "note": "same round trip on uniform-noise frames (every bit-plane of every code-block coded): the stress figure beside the smooth-frame headline"},
         "e2e_pageable": {"value": W * H / ((enc_ms_page + dec_ms_page) * 1e-3) / 1e6, "unit": "MPix/s", "encode_ms": enc_ms_page, "decode_ms": dec_ms_page,

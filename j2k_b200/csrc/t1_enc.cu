@@ -41,47 +41,36 @@ __device__ __forceinline__ int fix_mul_t1(int a, int b) {      // opj_intmath.h:
     return (int)(((long long)a * (long long)b + 4096) >> 18);
 }
 
-// sign-magnitude sample: bit 31 sign, 6 fractional bits (T1Encoder.cpp:139-171, t1_opt.h:169)
-__device__ __forceinline__ uint32_t load_smag(const T1Block& b, int x, int y) {
-    int v = __ldg(b.coeff + (size_t)y * b.pitch + x);
-    int t = b.qmfbid ? v * 64 : fix_mul_t1(v, b.bandconst);
-    uint32_t mag = (uint32_t)(t < 0 ? -t : t);
-    return mag | (t < 0 ? 0x80000000u : 0u);
+// sign-magnitude sample: bit 31 sign, 6 fractional bits (T1Encoder.cpp:139-171, t1_opt.h:169).  `mul` = the band's Q13 constant
+// for 9/7; for 5/3 the reference takes v * 64, which is the same fixed-point product with mul = 2^24 (v * 2^24 is a multiple of
+// 2^18, so the rounding term never carries): one path, no per-sample select.
+__device__ __forceinline__ int smag_mul(const T1Block& b) { return b.qmfbid ? (1 << 24) : b.bandconst; }
+__device__ __forceinline__ uint32_t to_smag(int v, int mul) {
+    const int t = fix_mul_t1(v, mul);
+    const uint32_t mag = (uint32_t)(t < 0 ? -t : t);
+    return mag | ((uint32_t)t & 0x80000000u);
+}
+__device__ __forceinline__ uint32_t load_smag(const T1Block& b, int x, int y, int mul) {
+    return to_smag(__ldg(b.coeff + (size_t)y * b.pitch + x), mul);
 }
 
-__device__ __forceinline__ int nmsedec_sig(const Luts& L, uint32_t mag, int bpno) {
-    return bpno > 0 ? L.nm_sig[(mag >> bpno) & 127] : L.nm_sig0[mag & 127];
+// nmsedec tables: plane 0 has tables of its own (t1_luts.h lut_nmsedec_sig0 / _ref0); they follow the general ones in Luts, so the
+// choice is an offset that is fixed per bit-plane (nm_off = bpno > 0 ? 0 : 128)
+__device__ __forceinline__ int nmsedec_sig(const Luts& L, uint32_t mag, int bpno, int nm_off) {
+    return (&L.nm_sig[0])[nm_off + ((mag >> bpno) & 127)];
 }
-__device__ __forceinline__ int nmsedec_ref(const Luts& L, uint32_t mag, int bpno) {
-    return bpno > 0 ? L.nm_ref[(mag >> bpno) & 127] : L.nm_ref0[mag & 127];
+__device__ __forceinline__ int nmsedec_ref(const Luts& L, uint32_t mag, int bpno, int nm_off) {
+    return (&L.nm_ref[0])[nm_off + ((mag >> bpno) & 127)];
 }
 
-// Byte-stream writer of one lane: symbols go out as aligned 32-bit words where the lane owns the
-// whole word, as single bytes at the ragged ends it shares with its neighbours.
-// bytes [from, to) of the word being assembled, one at a time: the ragged first / last word of a lane's piece.  Out of line on
-// purpose: inlined at every push it was 40 % of the kernel's code, which then no longer fitted the instruction cache.
-__device__ __noinline__ void store_ragged(uint8_t* base, uint32_t from, uint32_t to, uint32_t acc) {
-    for (uint32_t p = from; p < to; ++p) base[p] = (uint8_t)(acc >> ((p & 3) * 8));
-}
+// Symbol writer of one lane: one byte store per symbol.  (Assembling aligned 32-bit words per lane cost ten instructions per
+// symbol plus a ragged first / last word per piece -- 27 % of the kernel's instructions -- for pieces that are a few symbols
+// long; L2 merges the byte stores of a sector.)
 struct Emitter {
-    uint8_t* base;
-    uint32_t first, pos, acc;
-    __device__ void init(uint8_t* b, uint32_t start) { base = b; first = pos = start; acc = 0; }
-    __device__ __forceinline__ void push(uint32_t ctx, uint32_t d) {
-        acc |= ((ctx << 1) | d) << ((pos & 3) * 8);
-        ++pos;
-        if ((pos & 3) == 0) flush_word();
-    }
-    __device__ __forceinline__ void flush_word() {
-        const uint32_t w0 = pos - 4;
-        if (w0 >= first) *reinterpret_cast<uint32_t*>(base + w0) = acc;
-        else store_ragged(base, first, pos, acc);
-        acc = 0;
-    }
-    __device__ __forceinline__ void finish() {
-        const uint32_t w0 = pos & ~3u;
-        store_ragged(base, w0 > first ? w0 : first, pos, acc);
-    }
+    uint8_t* p;
+    __device__ __forceinline__ void init(uint8_t* b, uint32_t start) { p = b + start; }
+    __device__ __forceinline__ void push(uint32_t ctx, uint32_t d) { *p++ = (uint8_t)((ctx << 1) | d); }
+    __device__ __forceinline__ void finish() {}
 };
 
 enum { PASS_SIG = 0, PASS_REF = 1, PASS_CLN = 2 };
@@ -273,12 +262,24 @@ k_t1_context(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __
     const bool c0ok = lane < w, c1ok = lane + 32 < w;
 
     // ---- sweep 0: signs and the largest magnitude (T1Encoder.cpp:139-171) ----
+    const int mul = smag_mul(blk);
+    const int32_t* col0 = blk.coeff + (c0ok ? lane : 0);
+    const int32_t* col1 = blk.coeff + (c1ok ? lane + 32 : 0);
     uint32_t mx = 0;
-    for (int y = 0; y < h; ++y) {
-        const uint32_t m0 = c0ok ? load_smag(blk, lane, y) : 0u, m1 = c1ok ? load_smag(blk, lane + 32, y) : 0u;
-        mx = max(mx, max(m0 & 0x7fffffffu, m1 & 0x7fffffffu));
-        const uint32_t lo = __ballot_sync(FULL, m0 >> 31), hi = __ballot_sync(FULL, m1 >> 31);
-        if (lane == 0) R.sgn[y + 1] = (u64)lo | ((u64)hi << 32);
+    for (int y = 0; y < h; y += 2) {                       // two rows per turn: four loads in flight
+        const bool two = y + 1 < h;
+        const size_t o0 = (size_t)y * blk.pitch, o1 = (size_t)(two ? y + 1 : y) * blk.pitch;
+        const int v00 = __ldg(col0 + o0), v01 = __ldg(col1 + o0), v10 = __ldg(col0 + o1), v11 = __ldg(col1 + o1);
+        const uint32_t m00 = c0ok ? to_smag(v00, mul) : 0u, m01 = c1ok ? to_smag(v01, mul) : 0u;
+        const uint32_t m10 = c0ok ? to_smag(v10, mul) : 0u, m11 = c1ok ? to_smag(v11, mul) : 0u;
+        mx = max(mx, max(m00 & 0x7fffffffu, m01 & 0x7fffffffu));
+        const uint32_t lo0 = __ballot_sync(FULL, m00 >> 31), hi0 = __ballot_sync(FULL, m01 >> 31);
+        if (lane == 0) R.sgn[y + 1] = (u64)lo0 | ((u64)hi0 << 32);
+        if (two) {
+            mx = max(mx, max(m10 & 0x7fffffffu, m11 & 0x7fffffffu));
+            const uint32_t lo1 = __ballot_sync(FULL, m10 >> 31), hi1 = __ballot_sync(FULL, m11 >> 31);
+            if (lane == 0) R.sgn[y + 2] = (u64)lo1 | ((u64)hi1 << 32);
+        }
     }
     mx = __reduce_max_sync(FULL, mx);
     int numbps = mx ? (32 - __clz(mx)) - 6 : 0;               // t1_opt.cpp:680
@@ -299,17 +300,24 @@ k_t1_context(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __
     for (int bp = numbps - 1; bp >= 0 && !overflow; --bp) {
         const int one = bp + 6;
         const bool first = bp == numbps - 1;
+        const int nm_off = bp > 0 ? 0 : 128;
         // ---- sweep A: this plane's bits; distortion of refinement and of all newly significant ----
         int d_ref = 0, d_sig = 0;
-        for (int y = 0; y < h; ++y) {
-            const uint32_t m0 = c0ok ? (load_smag(blk, lane, y) & 0x7fffffffu) : 0u;
-            const uint32_t m1 = c1ok ? (load_smag(blk, lane + 32, y) & 0x7fffffffu) : 0u;
+        auto plane_row = [&](int y, uint32_t m0, uint32_t m1) {
             const uint32_t b0 = (m0 >> one) & 1u, b1 = (m1 >> one) & 1u;
             const uint32_t lo = __ballot_sync(FULL, b0), hi = __ballot_sync(FULL, b1);
             if (lane == 0) R.bit[y + 1] = (u64)lo | ((u64)hi << 32);
             const u64 s0 = R.sig[y + 1];
-            if ((s0 >> lane) & 1ull) d_ref += nmsedec_ref(L, m0, bp); else if (b0) d_sig += nmsedec_sig(L, m0, bp);
-            if ((s0 >> (lane + 32)) & 1ull) d_ref += nmsedec_ref(L, m1, bp); else if (b1) d_sig += nmsedec_sig(L, m1, bp);
+            if (!(lo | hi) && !s0) return;                 // warp-uniform: nothing refined, nothing becomes significant in this row
+            if ((s0 >> lane) & 1ull) d_ref += nmsedec_ref(L, m0, bp, nm_off); else if (b0) d_sig += nmsedec_sig(L, m0, bp, nm_off);
+            if ((s0 >> (lane + 32)) & 1ull) d_ref += nmsedec_ref(L, m1, bp, nm_off); else if (b1) d_sig += nmsedec_sig(L, m1, bp, nm_off);
+        };
+        for (int y = 0; y < h; y += 2) {
+            const bool two = y + 1 < h;
+            const size_t o0 = (size_t)y * blk.pitch, o1 = (size_t)(two ? y + 1 : y) * blk.pitch;
+            const int v00 = __ldg(col0 + o0), v01 = __ldg(col1 + o0), v10 = __ldg(col0 + o1), v11 = __ldg(col1 + o1);
+            plane_row(y, c0ok ? (to_smag(v00, mul) & 0x7fffffffu) : 0u, c1ok ? (to_smag(v01, mul) & 0x7fffffffu) : 0u);
+            if (two) plane_row(y + 1, c0ok ? (to_smag(v10, mul) & 0x7fffffffu) : 0u, c1ok ? (to_smag(v11, mul) & 0x7fffffffu) : 0u);
         }
         d_ref = __reduce_add_sync(FULL, d_ref);
         d_sig = __reduce_add_sync(FULL, d_sig);
@@ -358,8 +366,8 @@ k_t1_context(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __
             for (int y = 0; y < h; ++y) {
                 const u64 np = R.nsp[y + 1];
                 if (!np) continue;
-                if ((np >> lane) & 1ull) d_sp += nmsedec_sig(L, load_smag(blk, lane, y) & 0x7fffffffu, bp);
-                if ((np >> (lane + 32)) & 1ull) d_sp += nmsedec_sig(L, load_smag(blk, lane + 32, y) & 0x7fffffffu, bp);
+                if ((np >> lane) & 1ull) d_sp += nmsedec_sig(L, load_smag(blk, lane, y, mul) & 0x7fffffffu, bp, nm_off);
+                if ((np >> (lane + 32)) & 1ull) d_sp += nmsedec_sig(L, load_smag(blk, lane + 32, y, mul) & 0x7fffffffu, bp, nm_off);
             }
             d_sp = __reduce_add_sync(FULL, d_sp);
             if (lane == 0) { pn[passno] = n; res.nmsedec[passno] = d_sp; }
@@ -638,8 +646,9 @@ __global__ void __launch_bounds__(256) k_t1_gather(const T1Block* __restrict__ b
 void launch_t1_context(const T1Block* d_blocks, int nblocks, uint8_t* sym_arena, uint32_t* pass_nsym,
                        T1Result* results, cudaStream_t st) {
     if (nblocks <= 0) return;
-    // resident CTAs per SM the register allocation aims at (4: 124 registers, 5: 96, 6: 80 with a few spills); J2KCUDA_CX_MINB to compare
-    static const int minb = [] { const char* e = getenv("J2KCUDA_CX_MINB"); const int v = e ? atoi(e) : 4; return v < 4 ? 4 : v > 6 ? 6 : v; }();
+    // resident CTAs per SM the register allocation aims at (4: 126 registers, 5: 96, 6: 80 with a few spills).  Measured on B200, 4K RGBA16:
+    // 1.57 / 1.49 / 1.46 ms alone, 2276 / 2236 / 2413 MPix/s encode with 16 frames in flight: 6 is the default; J2KCUDA_CX_MINB to compare
+    static const int minb = [] { const char* e = getenv("J2KCUDA_CX_MINB"); const int v = e ? atoi(e) : 6; return v < 4 ? 4 : v > 6 ? 6 : v; }();
     const dim3 grid((nblocks + CX_WARPS - 1) / CX_WARPS), block(32 * CX_WARPS);
     if (minb == 4) k_t1_context<4><<<grid, block, 0, st>>>(d_blocks, nblocks, t1_tables_device(), sym_arena, pass_nsym, results);
     else if (minb == 5) k_t1_context<5><<<grid, block, 0, st>>>(d_blocks, nblocks, t1_tables_device(), sym_arena, pass_nsym, results);

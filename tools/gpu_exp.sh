@@ -17,7 +17,9 @@ decprof)   # ncu full capture of the Tier-1 decode kernel of one 4K frame: tools
   env "$@" python tools/dec_bench.py --frames 1 --alone-only --tag $name > gpurun_out/${name}_plain.log 2>&1 &&
   env "$@" ncu --set full --clock-control none --import-source on -k regex:k_t1_decode -s 2 -c 1 -f -o gpurun_out/$name \
       python tools/dec_bench.py --frames 1 --alone-only --tag $name > gpurun_out/${name}_ncu.log 2>&1
-  cat gpurun_out/${name}_plain.log; tail -3 gpurun_out/${name}_ncu.log ;;
+  python tools/ncu_summary.py gpurun_out/$name.ncu-rep > gpurun_out/${name}_summary.txt 2>&1
+  python tools/ncu_lines.py gpurun_out/$name.ncu-rep k_t1_decode 70 > gpurun_out/${name}_lines.txt 2>&1
+  cat gpurun_out/${name}_plain.log; tail -3 gpurun_out/${name}_ncu.log; head -60 gpurun_out/${name}_lines.txt ;;
 dwtsweep)  # per-level tunables of the DWT kernels (J2KCUDA_DWT_*), forward and inverse totals of one 4K RGBA16 frame
   : > gpurun_out/dwtsweep.log
   for cfg in "" "J2KCUDA_DWT_MINSP=4" "J2KCUDA_DWT_MINSP=2" "J2KCUDA_DWT_MINSP=4 J2KCUDA_DWT_FLOOR=4736" "J2KCUDA_DWT_MINSP=4 J2KCUDA_DWT_FLOOR=9472" \
@@ -32,6 +34,13 @@ bench)     # bench.py on this box: tools/gpu_exp.sh bench <name> [bench.py args.
   name=${2:-bench}; shift 2
   python bench.py "$@" > gpurun_out/$name.json 2> gpurun_out/$name.err; tail -2 gpurun_out/$name.err
   python tools/bench_summary.py gpurun_out/$name.json ;;
+cxprof)    # ncu full capture of k_t1_context of one 4K frame: tools/gpu_exp.sh cxprof <name> [env assignments...]
+  name=${2:-cx}; shift 2
+  env "$@" ncu --set full --clock-control none --import-source on -k regex:k_t1_context -s 2 -c 1 -f -o gpurun_out/$name \
+      python tools/stage_times.py dwt > gpurun_out/${name}_ncu.log 2>&1
+  python tools/ncu_summary.py gpurun_out/$name.ncu-rep > gpurun_out/${name}_summary.txt 2>&1
+  python tools/ncu_lines.py gpurun_out/$name.ncu-rep k_t1_context 60 > gpurun_out/${name}_lines.txt 2>&1
+  cat gpurun_out/${name}_summary.txt; head -40 gpurun_out/${name}_lines.txt ;;
 cxsweep)   # resident CTAs of k_t1_context (J2KCUDA_CX_MINB): per-stage times alone and the batch throughput
   : > gpurun_out/cxsweep.log
   for mb in 4 5 6; do
