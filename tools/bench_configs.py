@@ -249,7 +249,7 @@ def main():
 
     jobs = [
         ("C4api", lambda: run_tiles_api("C4 8192x4320 16-bit RGB lossless, 1024x1024 tiles, j2kcuda_tiles_* in one process", 4320, 8192, 3, 16, 1024, args.frames8k)),
-        ("C5api", lambda: run_sequence_api("C5 4096x2160 16-bit RGB lossless sequence, j2kcuda_sequence_create_multi in one process", 2160, 4096, 3, 16, 16, mct=1)),
+        ("C5api", lambda: run_sequence_api("C5 4096x2160 16-bit RGB lossless sequence, j2kcuda_sequence_create_multi in one process", 2160, 4096, 3, 16, 8, mct=1)),
         ("C1", lambda: run_sequence("C1 2048x1080 8-bit RGB lossless 5/3", 1080, 2048, 3, 8, 16, True, mct=1)),
         ("C2", lambda: run_sequence("C2 4096x2160 16-bit RGBA lossless 5/3", 2160, 4096, 4, 16, 8, True, mct=1)),
         ("C3", lambda: run_sequence("C3 DCI 4K 12-bit XYZ 9/7 ICT cinema profile (PCRD rate cap)", 2160, 4096, 3, 12, 8, False,
