@@ -29,8 +29,10 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 W, H, NC, PREC = 4096, 2160, 4, 16
 WORKLOAD = "4096x2160 16-bit RGBA lossless 5/3 (RCT, 6 resolutions, 64x64 code-blocks, 1 tile)"
-FRAMES = 16  # frames per step per GPU (one batch of the image sequence): 16 x 70.8 MB of input and 283 MB of
-             # planes per frame in flight -- far beyond the 126 MB L2, so no flush is needed between steps
+FRAMES = 32  # frames per step per GPU (one batch of the image sequence): 32 x 70.8 MB of input and 283 MB of planes per
+             # frame in flight -- far beyond the 126 MB L2, so no flush is needed between steps.  Round 1 used 16 = one frame per
+             # worker and phase; with two, the host Tier-2 of the first wave overlaps the kernels of the second (BASELINE C5 is a
+             # 240-frame sequence: the steady state is what the path runs in)
 TRAFFIC_L1 = 239819520  # dram__bytes_read.sum 142 357 760 + dram__bytes_write.sum 97 461 760 of one level-1 launch, from the
                         # ncu --set full capture in profiles/r2_frame_full_raw.csv.gz (part of the 141.6 MB written stays in L2)
 WORKERS = 16  # contexts (stream + buffers + host thread) the sequence keeps in flight
@@ -44,22 +46,50 @@ def peaks():
 
 
 class ClockSampler(threading.Thread):
-    def __init__(self, index):
+    """SM clock and throttle reasons of this rank's GPU every 200 ms DURING the timed region (B200_PROFILING.md's clocks line).
+    Read through NVML inside the process (what nvidia-smi itself calls); if the binding is missing, ONE `nvidia-smi -lms 200`
+    loop process.  (Round 1 spawned a fresh nvidia-smi per sample from every rank: at 8 ranks those start-ups, each of which
+    opens all 8 GPUs, slowed the CUDA calls of every rank.)"""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index, uuid=None):
         super().__init__(daemon=True)
-        self.index, self.rows, self.stop = index, [], False
+        self.index, self.uuid, self.rows, self.stop, self.how = index, uuid, [], False, "nvml"
+
+    def run_nvml(self):
+        import pynvml as N
+        N.nvmlInit()
+        h = N.nvmlDeviceGetHandleByUUID(self.uuid) if self.uuid else N.nvmlDeviceGetHandleByIndex(self.index)   # CUDA_VISIBLE_DEVICES-proof
+        bits = [N.nvmlClocksThrottleReasonHwSlowdown, N.nvmlClocksThrottleReasonHwThermalSlowdown,
+                N.nvmlClocksThrottleReasonSwThermalSlowdown, N.nvmlClocksThrottleReasonSwPowerCap]
+        while not self.stop:
+            r = N.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+            self.rows.append([str(N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM)), str(N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM))] +
+                             ["Active" if r & b else "Not Active" for b in bits])
+            time.sleep(0.2)
+
+    def run_smi(self):
+        self.how = "nvidia-smi -lms 200"
+        p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "200"],
+                             stdout=subprocess.PIPE, text=True)
+        try:
+            for line in p.stdout:
+                if self.stop:
+                    break
+                if line.strip():
+                    self.rows.append([x.strip() for x in line.split(",")])
+        finally:
+            p.kill()
 
     def run(self):
-        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
-            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
-        while not self.stop:
+        try:
+            self.run_nvml()
+        except Exception:
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
+                self.run_smi()
             except Exception:
                 pass
-            time.sleep(0.2)
 
     def summary(self):
         sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
@@ -67,7 +97,7 @@ class ClockSampler(threading.Thread):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(self.rows)}
+                "samples": len(self.rows), "how": self.how}
 
 
 def reference_encode_fn():
@@ -135,8 +165,9 @@ def main():
         return
     if args.workers <= 0:
         # frames in flight per GPU: enough to keep the Tier-1 kernels of several frames on the device while other frames are in
-        # host Tier-2, but no more host threads than the box has cores for (8 ranks x 16 workers on 32 cores cost 20 % at N = 8)
-        args.workers = max(6, min(WORKERS, (os.cpu_count() or 16) // max(world, 1)))
+        # host Tier-2.  The workers sleep while the device works (blocking event waits), so a rank may have more of them than cores:
+        # on 4 cores 16 workers still beat 6 (profiles/r2_cpuexp.log); the cap only bounds the thread count on small hosts
+        args.workers = WORKERS if world <= 2 else max(8, min(WORKERS, 3 * (os.cpu_count() or 16) // world))
 
     import torch
     import torch.distributed as dist
@@ -213,6 +244,8 @@ def main():
         lib.j2kcuda_sequence_stats(seq, em, ec, dm, dc, fr, 1 if reset else 0)
         return np.array(list(em)), list(ec), np.array(list(dm)), list(dc), list(fr)
 
+    per_rank_ms = []          # ms per step of every rank, one list per timed() call (device-resident, then host buffers)
+
     def timed(flags, tin, tout):
         for _ in range(args.warmup):
             step(flags, tin, tout)
@@ -233,10 +266,13 @@ def main():
         t = torch.tensor([e0.elapsed_time(e1)], device="cuda")
         if world > 1:
             dist.barrier()
+            every = [torch.zeros_like(t) for _ in range(world)]
+            dist.all_gather(every, t)
+            per_rank_ms.append([round(float(x.item()) / args.steps, 2) for x in every])
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()), nbytes / (args.steps * F), tdec / args.steps * 1e3, stats(True)
 
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(local, "GPU-" + str(torch.cuda.get_device_properties(local).uuid))
     sampler.start()
     t_dev, cs_bytes, dec_ms_dev, st_dev = timed(1, dev_in, dev_out)          # J2KCUDA_SEQ_DEVICE_PIXELS
     for i in range(F):
@@ -437,6 +473,7 @@ def main():
                "decode_code_blocks_per_s_alone": nblocks / (solo_dec[2] * 1e-3),
                "code_blocks_per_s_job": world * args.steps * F * nblocks / (t_dev * 1e-3)},
         "clocks": sampler.summary(),
+        "per_rank_ms_per_step": per_rank_ms,
     }
     if not args.no_cpu_baseline:
         fn, kind, cores = reference_encode_fn()

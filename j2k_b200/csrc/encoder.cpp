@@ -67,6 +67,7 @@ struct j2kcuda_encoder {
     T1Result* h_results = nullptr;                   // pinned
     uint32_t* h_offsets = nullptr;                   // pinned
     uint8_t* h_packed = nullptr; size_t h_packed_cap = 0;   // pinned
+    size_t last_packed = 0;          // packed bytes of the previous frame of this context: sizes the speculative D2H
     std::vector<std::vector<double>> dist;           // per block cumulative distortion
     int mq_lanes = 4;
     uint32_t* d_mq_order = nullptr; int mq_nlong = 592;  // MQ kernel: blocks by decreasing symbol count, at most mq_nlong of the longest get a warp each
@@ -519,6 +520,18 @@ int j2kcuda_encoder_run(j2kcuda_encoder* e) { return j2k::guarded([&]() -> int {
         CK(cudaMemcpyAsync(e->h_results, e->d_results, (size_t)e->nblocks * sizeof(T1Result), cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(e->h_offsets, e->d_offsets, ((size_t)e->nblocks + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     }
+    // The packed code bytes follow in the same wait: their size is only known on the device at this point, so the copy is sized
+    // from the previous frame of this context (+6 %, frames of a sequence differ by a few percent); the rare remainder is
+    // fetched afterwards.  One blocking wait per frame instead of two: on a busy host every wake-up costs scheduler latency.
+    size_t guess = 0;
+    static const bool speculate = [] { const char* v = getenv("J2KCUDA_SPEC_D2H"); return !(v && v[0] == '0'); }();
+    if (speculate && e->nblocks && e->last_packed && e->h_packed) {
+        guess = e->last_packed + e->last_packed / 16 + 65536;
+        if (guess > e->h_packed_cap) guess = e->h_packed_cap;
+        if (guess > e->out_bytes) guess = e->out_bytes;
+        if (guess) CK(cudaMemcpyAsync(e->h_packed, e->d_packed, guess, cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaEventRecord(e->ev[5], st));
     CK(stream_wait(st, e->ev_wait));
     CK(cudaGetLastError());
     size_t packed = e->nblocks ? e->h_offsets[e->nblocks] : 0;
@@ -527,10 +540,14 @@ int j2kcuda_encoder_run(j2kcuda_encoder* e) { return j2k::guarded([&]() -> int {
         size_t cap = packed + packed / 4 + 4096;
         CK(cudaMallocHost(&e->h_packed, cap));
         e->h_packed_cap = cap;
+        guess = 0;
     }
-    if (packed) CK(cudaMemcpyAsync(e->h_packed, e->d_packed, packed, cudaMemcpyDeviceToHost, st));
-    CK(cudaEventRecord(e->ev[5], st));
-    CK(stream_wait(st, e->ev_wait));
+    if (packed > guess) {
+        CK(cudaMemcpyAsync(e->h_packed + guess, e->d_packed + guess, packed - guess, cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(e->ev[5], st));
+        CK(stream_wait(st, e->ev_wait));
+    }
+    e->last_packed = packed;
     uint64_t nsym = 0;
     for (int i = 0; i < e->nblocks; ++i) {
         if (e->h_results[i].status != 0)
