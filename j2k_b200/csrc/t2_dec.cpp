@@ -259,8 +259,13 @@ static bool read_packet(const CodingParams& cp, DecTile& t, const PacketId& pk, 
                 else included = bio.getbit();
                 if (!included) continue;
                 if (!cb.included) {
-                    int i = 1;
-                    while (!t.imsb[ti].decode(bio, k, i)) { if (++i > 75 || bio.overrun) { err = "bad zero bit-plane count"; return false; } }
+                    // The reference asks the tag tree "is the value below i?" for i = 1, 2, ... (t2.cpp:1226-1236), walking the tree
+                    // once per question.  A node's bits are only read once all its ancestors are known, so one walk with the largest
+                    // threshold the loop would reach reads the very same bits in the same order and leaves the value behind.
+                    t.imsb[ti].decode(bio, k, 76);
+                    const int zbp = t.imsb[ti].nodes[k].value;
+                    if (zbp >= 75 || bio.overrun) { err = "bad zero bit-plane count"; return false; }
+                    const int i = zbp + 1;
                     cb.numbps = band.numbps + 1 - i;
                     cb.numlenbits = 3;
                     cb.included = true;

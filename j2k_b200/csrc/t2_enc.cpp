@@ -178,6 +178,19 @@ static void makelayer(const CodingParams& cp, EncTile& t, int layno, double thre
         EncLayer& layer = cblk.layers[layno];
         if (layno == 0) cblk.included_other = 0;
         int n = cblk.included_other;
+        if (lossless && !include_all) {
+            // every pass whose rate grows is in (no slope can be below the tile's smallest), a pass with no new bytes only when
+            // it changes the distortion: by induction a pass is left out exactly when its cumulative (rate, distortion) equals
+            // the previous pass's, so the layer ends at the last pass that differs from its predecessor -- found from the end
+            int p = cblk.totalpasses - 1;
+            const int32_t r0 = n ? cblk.rates[n - 1] : 0; const double d0 = n ? cblk.dist[n - 1] : 0.0;
+            while (p >= n) {
+                const int32_t rp = p > n ? cblk.rates[p - 1] : r0; const double dp = p > n ? cblk.dist[p - 1] : d0;
+                if (cblk.rates[p] != rp || cblk.dist[p] != dp) break;
+                --p;
+            }
+            n = p + 1 > n ? p + 1 : n;
+        } else
         for (int passno = cblk.included_other; passno < cblk.totalpasses; ++passno) {
             uint32_t dr; double dd;
             if (n == 0) { dr = (uint32_t)cblk.rates[passno]; dd = cblk.dist[passno]; }

@@ -1,5 +1,6 @@
 """One-line summaries of bench.py JSON lines (files given on the command line)."""
-import json, sys
+import json, signal, sys
+signal.signal(signal.SIGPIPE, signal.SIG_DFL)   # | head
 for f in sys.argv[1:]:
     try:
         d = json.loads(open(f).read().strip().splitlines()[-1])
