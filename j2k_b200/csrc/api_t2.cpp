@@ -95,6 +95,7 @@ int j2kcuda_t2_block_structure(const j2kcuda_params* p, int32_t* out, int max_bl
 int j2kcuda_t2_assemble(const j2kcuda_params* p, const j2kcuda_block_result* blocks, int nblocks,
                         uint8_t** out, size_t* out_len) { return j2k::guarded([&]() -> int {
     if (!p || !blocks || !out || !out_len) return set_error(J2KCUDA_ERR_PARAM, "null argument");
+    if (const char* why = check_params(*p)) return set_error(J2KCUDA_ERR_PARAM, why);
     EncoderHost host;
     setup_coding_params(*p, host.cp);
     int nt = (int)(host.cp.tw * host.cp.th);

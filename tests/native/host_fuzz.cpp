@@ -15,7 +15,78 @@
 #include <vector>
 using namespace j2k;
 static std::vector<std::vector<uint8_t>> seeds;
+// ---- second mode: host Tier-2 writer -> host parser over random geometry ------------------------------------------------
+// Random (valid or refused) parameters, random code-block results; whatever j2kcuda_t2_assemble writes, DecoderHost::parse must
+// read back: per code-block the same bit-plane count, a pass count the writer could have chosen, and exactly the bytes of
+// those passes.  tests/native/host_fuzz --roundtrip <seconds> <rng seed>
+static int roundtrip(double seconds, unsigned seed0) {
+    std::mt19937 rng(seed0);
+    auto t0 = std::chrono::steady_clock::now();
+    long iters = 0, written = 0, refused = 0;
+    while (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() < seconds) {
+        ++iters;
+        j2kcuda_params p; j2kcuda_default_params(&p);
+        p.width = 1 + rng() % 300; p.height = 1 + rng() % 300; p.ncomp = 1 + rng() % 4; p.prec = 1 + rng() % 16;
+        p.irreversible = rng() & 1; p.numresolution = 1 + rng() % 7; p.mct = (p.ncomp >= 3) ? (rng() & 1) : 0;
+        const int cw = 2 + rng() % 5, chmax = 12 - cw < 6 ? 12 - cw : 6, ch = 2 + rng() % (chmax - 1);
+        p.cblk_w = 1u << cw; p.cblk_h = 1u << ch;
+        p.prog_order = rng() % 5;
+        if (rng() % 3 == 0) { p.tile_w = 16 + rng() % 200; p.tile_h = 16 + rng() % 200; }
+        p.numlayers = 1 + rng() % 4;
+        const bool lossy = rng() % 2;
+        for (unsigned k = 0; k < p.numlayers; ++k) p.rates[k] = lossy ? (k + 1 == p.numlayers && (rng() & 1) ? 0.0 : 40.0 / (k + 1) + (rng() % 10)) : 0.0;
+        p.compat = rng() % 3;
+        const int nb = j2kcuda_t2_block_count(&p);
+        if (nb < 0) { ++refused; continue; }
+        if (nb == 0 || nb > 20000) continue;
+        std::vector<j2kcuda_block_result> res((size_t)nb);
+        std::vector<std::vector<int32_t>> rates((size_t)nb);
+        std::vector<std::vector<double>> dist((size_t)nb);
+        std::vector<std::vector<uint8_t>> data((size_t)nb);
+        std::vector<int32_t> geo(12 * (size_t)nb);
+        if (j2kcuda_t2_block_geometry(&p, geo.data(), nb) != nb) { printf("block geometry disagrees with block count\n"); return 2; }
+        for (int i = 0; i < nb; ++i) {
+            const int band_bps = geo[12 * (size_t)i + 8];             // a block never has more bit-planes than its band (t1_opt.cpp:680)
+            int numbps = (rng() % 5 == 0) ? 0 : 1 + rng() % 12;
+            if (numbps > band_bps) numbps = band_bps > 0 ? band_bps : 0;
+            const int np = numbps ? 1 + rng() % (3 * numbps - 2) : 0;
+            int r = 0; double dd = 0;
+            rates[i].resize(np + 1); dist[i].resize(np + 1);
+            for (int k = 0; k < np; ++k) { r += (rng() % 4 == 0) ? 0 : rng() % 40; dd += (rng() % 4 == 0) ? 0.0 : (double)(rng() % 100000); rates[i][k] = r; dist[i][k] = dd; }
+            data[i].resize((size_t)r + 4);
+            for (auto& b : data[i]) b = (uint8_t)(rng() % 255);           // no 0xFF: bodies never look like markers
+            res[i].data = data[i].data(); res[i].numbps = numbps; res[i].npasses = np; res[i].rates = rates[i].data(); res[i].dist = dist[i].data();
+        }
+        uint8_t* out = nullptr; size_t n = 0;
+        if (j2kcuda_t2_assemble(&p, res.data(), nb, &out, &n) != 0) { ++refused; continue; }
+        ++written;
+        DecoderHost h; std::string err;
+        if (!h.parse(out, n, err)) { printf("parser refused the writer's stream: %s\n", err.c_str()); return 2; }
+        int k = 0;
+        for (auto& t : h.tiles)
+            for (auto& b : t.blocks) {
+                if (k >= nb) { printf("more blocks read than written\n"); return 2; }
+                if (b.included) {
+                    if (b.numbps != res[k].numbps || b.npasses < 1 || b.npasses > res[k].npasses || b.len != rates[k][b.npasses - 1]) {
+                        printf("block %d: numbps %d/%d passes %d/%d len %d\n", k, b.numbps, res[k].numbps, b.npasses, res[k].npasses, b.len); return 2;
+                    }
+                    size_t pos = 0;
+                    for (auto& c : b.chunks) { if (memcmp(out + c.first, data[k].data() + pos, c.second)) { printf("block %d: bytes differ\n", k); return 2; } pos += c.second; }
+                    if ((int)pos != b.len) { printf("block %d: chunks do not add up\n", k); return 2; }
+                } else if (b.len != 0) { printf("block %d: bytes without inclusion\n", k); return 2; }
+                ++k;
+            }
+        if (k != nb) { printf("%d blocks read, %d written\n", k, nb); return 2; }
+        j2kcuda_free(out);
+    }
+    printf("%ld iterations, %ld written and read back, %ld refused\n", iters, written, refused);
+    fflush(stdout);
+    j2k::out_release_all();          // the recycled output buffers (what j2kcuda_shutdown does)
+    return written > 0 ? 0 : 3;
+}
+
 int main(int argc, char** argv) {
+    if (argc > 1 && !strcmp(argv[1], "--roundtrip")) return roundtrip(argc > 2 ? atof(argv[2]) : 10, argc > 3 ? atoi(argv[3]) : 1);
     const char* dir = argc > 1 ? argv[1] : ".";
     double seconds = argc > 2 ? atof(argv[2]) : 60;
     unsigned seed0 = argc > 3 ? atoi(argv[3]) : 1;
@@ -61,4 +132,5 @@ int main(int argc, char** argv) {
         ++iters;
     }
     printf("%ld iterations, %ld parsed ok\n", iters, ok);
+    fflush(stdout);
 }

@@ -46,3 +46,13 @@ def test_decoder_block_routine_stays_inside_the_arena_contract():
     r = subprocess.run([exe, "5", "99"], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, (r.stdout[-300:], r.stderr[-3000:])
     assert int(r.stdout.split()[0]) > 500
+
+
+def test_host_writer_and_parser_agree_over_random_geometry(fuzzer):
+    """random image / tile / precinct-free geometry, code-block shapes, layers, rates, progression orders and compat modes with random
+    code-block results: whatever the Tier-2 writer emits, the parser reads back per block the same bit-plane count, a pass count
+    the writer could have chosen and exactly those passes' bytes (host_fuzz --roundtrip, under ASan + UBSan)."""
+    r = subprocess.run([fuzzer, "--roundtrip", "6", "7"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, (r.stdout[-500:], r.stderr[-3000:])
+    nums = [int(x) for x in r.stdout.replace(",", " ").split() if x.isdigit()]
+    assert nums[1] > 50
