@@ -77,6 +77,37 @@ static int roundtrip(double seconds, unsigned seed0) {
                 ++k;
             }
         if (k != nb) { printf("%d blocks read, %d written\n", k, nb); return 2; }
+        // the same stream inside JP2 boxes (j2kcuda_wrap_jp2) must be found again, with what the boxes say (j2kcuda_probe_jp2)
+        if (p.ncomp <= 4) {
+            j2kcuda_jp2_params jp; memset(&jp, 0, sizeof(jp));
+            jp.width = p.width; jp.height = p.height; jp.ncomp = p.ncomp;
+            const bool mixed = rng() % 4 == 0;
+            const unsigned sg = rng() & 1;        // one sign for all: like the reference, the writer falls back to bpcc only when DEPTHS differ (jp2.cpp:2115-2124)
+            for (unsigned c = 0; c < p.ncomp; ++c) { jp.prec[c] = mixed ? 1 + rng() % 16 : p.prec; jp.sgnd[c] = sg; }
+            jp.enumcs = p.ncomp >= 3 ? 16 : 17;
+            std::vector<uint8_t> icc;
+            if (rng() % 3 == 0) { icc.resize(128 + rng() % 600); for (auto& b : icc) b = (uint8_t)rng(); jp.icc = icc.data(); jp.icc_len = icc.size(); }
+            jp.alpha_comp = (p.ncomp == 2 || p.ncomp == 4) && (rng() & 1) ? (int)p.ncomp - 1 : -1;
+            uint8_t* boxed = nullptr; size_t bn = 0;
+            if (j2kcuda_wrap_jp2(out, n, &jp, &boxed, &bn) != 0) { printf("wrap_jp2 refused: %s\n", j2kcuda_last_error()); return 2; }
+            j2kcuda_jp2_info ji;
+            if (j2kcuda_probe_jp2(boxed, bn, &ji) != 0 || !ji.is_jp2) { printf("probe_jp2 refused the wrapper's file: %s\n", j2kcuda_last_error()); return 2; }
+            if (ji.width != p.width || ji.height != p.height || ji.ncomp != p.ncomp || ji.codestream_length != n ||
+                ji.codestream_offset + n > bn || memcmp(boxed + ji.codestream_offset, out, n)) { printf("jp2: header or codestream differs\n"); return 2; }
+            for (unsigned c = 0; c < p.ncomp; ++c)
+                if (ji.bpcc[c] != ((jp.prec[c] - 1) | (jp.sgnd[c] << 7))) { printf("jp2: bpcc of component %u differs\n", c); return 2; }
+            if (jp.icc) { if (ji.colr_method != 2 || ji.icc_length != jp.icc_len || memcmp(boxed + ji.icc_offset, jp.icc, jp.icc_len)) { printf("jp2: ICC profile differs\n"); return 2; } }
+            else if (ji.colr_method != 1 || ji.enumcs != jp.enumcs) { printf("jp2: colour specification differs\n"); return 2; }
+            if (jp.alpha_comp >= 0 && !jp.icc) {      // (with an ICC profile the reference writes no cdef either: jp2.cpp:2173-2181)
+                bool found = false;
+                for (unsigned i = 0; i < ji.cdef_n; ++i) if (ji.cdef_cn[i] == (unsigned)jp.alpha_comp && ji.cdef_typ[i] == 1) found = true;
+                if (!found) { printf("jp2: opacity channel not declared\n"); return 2; }
+            }
+            // and through the decoder's own locator
+            size_t off = 0, len = 0; bool isjp2 = false;
+            if (!find_codestream(boxed, bn, off, len, isjp2) || !isjp2 || off != ji.codestream_offset || len != n) { printf("find_codestream disagrees with probe_jp2\n"); return 2; }
+            j2kcuda_free(boxed);
+        }
         j2kcuda_free(out);
     }
     printf("%ld iterations, %ld written and read back, %ld refused\n", iters, written, refused);
