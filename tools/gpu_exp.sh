@@ -49,4 +49,23 @@ cxsweep)   # resident CTAs of k_t1_context (J2KCUDA_CX_MINB): per-stage times al
     J2KCUDA_CX_MINB=$mb python bench.py --steps 3 --warmup 2 --no-cpu-baseline 2>/dev/null | python tools/bench_summary.py /dev/stdin | head -1 >> gpurun_out/cxsweep.log
   done
   cat gpurun_out/cxsweep.log ;;
+cpuexp)    # host cores against frames in flight (profiles/r2_cpuexp.log): taskset to 4 and 2 cores, 6 and 16 workers, 32 frames per step
+  : > gpurun_out/cpuexp.log; nproc >> gpurun_out/cpuexp.log
+  run() { echo "== $*" >> gpurun_out/cpuexp.log; "$@" 2>/dev/null | python tools/bench_summary.py /dev/stdin 2>/dev/null | head -5 | cut -c1-330 >> gpurun_out/cpuexp.log; }
+  B="python bench.py --steps 3 --warmup 2 --no-cpu-baseline --frames 16"
+  run $B --workers 16; run $B --workers 6; run taskset -c 0-3 $B --workers 6; run taskset -c 0-3 $B --workers 16
+  run taskset -c 0-1 $B --workers 16; run python bench.py --steps 3 --warmup 2 --no-cpu-baseline --workers 16 --frames 32
+  cat gpurun_out/cpuexp.log ;;
+mqexp)     # one-block warps of the MQ encoder (J2KCUDA_MQ_NLONG, profiles/r2_mqexp.log)
+  : > gpurun_out/mqexp.log
+  for nl in ${NLONGS:-0 64}; do
+    echo "== J2KCUDA_MQ_NLONG=$nl" >> gpurun_out/mqexp.log
+    J2KCUDA_MQ_NLONG=$nl python bench.py --steps 3 --warmup 2 --no-cpu-baseline 2>/dev/null | python tools/bench_summary.py /dev/stdin 2>/dev/null | head -4 | cut -c1-300 >> gpurun_out/mqexp.log
+  done
+  cat gpurun_out/mqexp.log ;;
+check)     # the two things the round's end runs: GPU tests and the bench line: tools/gpu_exp.sh check <tag>
+  tag=${2:-check}
+  python -m pytest tests -m gpu -q 2>&1 | tail -6 > gpurun_out/${tag}_gpu_tests.log
+  python bench.py > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err
+  cat gpurun_out/${tag}_gpu_tests.log; python tools/bench_summary.py gpurun_out/${tag}_bench.json ;;
 esac
