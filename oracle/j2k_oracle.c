@@ -257,7 +257,10 @@ static void mqe_renorm(mqenc_t* q) {                        /* mqc.cpp:259-269 *
         if (q->ct == 0) mqe_byteout(q);
     } while ((q->a & 0x8000) == 0);
 }
+/* optional trace of the (context, decision) sequence: what the CUDA context kernel hands to its MQ kernels */
+static uint8_t* g_trace = NULL; static int g_trace_cap = 0, g_trace_n = 0;
 static void mqe_encode(mqenc_t* q, int ctx, uint32_t d) {   /* mqc.cpp:271-297, 428-439 */
+    if (g_trace) { if (g_trace_n < g_trace_cap) g_trace[g_trace_n] = (uint8_t)((ctx << 1) | d); ++g_trace_n; }
     uint32_t s = q->st[ctx], qe = MQ_QE[s];
     q->a -= qe;
     if (q->mps[ctx] == d) {
@@ -504,6 +507,62 @@ int orc_t1_encode_cblk(const uint32_t* smag, int w, int h, int orient, uint32_t 
     int total = mqe_numbytes(&q);
     const uint8_t* data = buf + 1;
     for (int i = 0; i < passno; ++i) {                   /* t1_opt.cpp:727-736 */
+        if (rates[i] > total) rates[i] = total;
+        if (rates[i] > 1 && data[rates[i] - 1] == 0xFF) rates[i]--;
+    }
+    int used = passno ? rates[passno - 1] : 0;
+    int rc = used;
+    if (used > cap) rc = -1; else memcpy(out, data, (size_t)used);
+    free(buf); t1s_free(&s);
+    return rc;
+}
+
+/* The GENERIC encoder loop (t1.cpp:1537-1673) for the code-block styles that only touch the arithmetic coder: RESET (0x02,
+ * contexts back to their initial states after every pass) and TERMALL (0x04, the coder is flushed and restarted after every
+ * pass: every pass is a codeword segment of its own).  Context modelling is that of cblksty == 0.  Differences from the
+ * optimised loop above: the rate of a pass is numbytes + 3, or + 1 when the pass was terminated, and only when numbytes > 0;
+ * the restart steps back over the last byte (mqc.cpp:521-532) and the final flush comes on top of the last pass's own.
+ * Optional outputs: the symbol trace ((ctx << 1) | d per decision) and the number of symbols of every pass. */
+int orc_t1_encode_cblk_sty(const uint32_t* smag, int w, int h, int orient, uint32_t maxmag, int cblksty,
+                           uint8_t* out, int cap, int* numbps, int* npasses, int* rates, int* nmsedec,
+                           uint8_t* trace, int trace_cap, uint32_t* pass_nsym) {
+    if (cblksty & ~0x06) return -2;
+    nm_init();
+    t1state_t s;
+    if (t1s_init(&s, w, h)) return -1;
+    int worst = w * h * 8 + 64;
+    uint8_t* buf = (uint8_t*)calloc(1, (size_t)worst + 2);
+    mqenc_t q;
+    mqe_init(&q, buf + 1);
+    int nb = maxmag ? floorlog2(maxmag) + 1 - 6 : 0;
+    if (nb < 0) nb = 0;
+    *numbps = nb;
+    g_trace = trace; g_trace_cap = trace_cap; g_trace_n = 0;
+    int bpno = nb - 1, passtype = 2, passno = 0;
+    for (; bpno >= 0; ++passno) {
+        int nm = 0, before = g_trace_n, correction = 3;
+        if (passtype == 0) enc_sigpass(&s, &q, smag, bpno, orient, &nm);
+        else if (passtype == 1) enc_refpass(&s, &q, smag, bpno, &nm);
+        else enc_clnpass(&s, &q, smag, bpno, orient, &nm);
+        nmsedec[passno] = nm;
+        if (pass_nsym) pass_nsym[passno] = (uint32_t)(g_trace_n - before);
+        if (cblksty & 0x04) {                                   /* t1.cpp:1618-1647 */
+            mqe_flush(&q);
+            correction = 1;
+            q.a = 0x8000; q.c = 0; q.ct = 12; q.bp--;           /* opj_mqc_restart_init_enc, mqc.cpp:521-532 */
+            if (q.bp >= q.start - 1 && *q.bp == 0xff) q.ct = 13;
+        }
+        if (++passtype == 3) { passtype = 0; bpno--; }
+        rates[passno] = mqe_numbytes(&q);
+        if (rates[passno] > 0) rates[passno] += correction;
+        if (cblksty & 0x02) mq_reset(q.st, q.mps);              /* t1.cpp:1654-1656 */
+    }
+    g_trace = NULL;
+    mqe_flush(&q);                                              /* t1.cpp:1659-1663 (no PTERM, no LAZY) */
+    *npasses = passno;
+    int total = mqe_numbytes(&q);
+    const uint8_t* data = buf + 1;
+    for (int i = 0; i < passno; ++i) {                          /* t1.cpp:1667-1677 */
         if (rates[i] > total) rates[i] = total;
         if (rates[i] > 1 && data[rates[i] - 1] == 0xFF) rates[i]--;
     }

@@ -81,3 +81,10 @@ extern "C" int t1dec_host_block_gen(const uint8_t* data, const int* seg_len, con
     decode_block<true>(b, R, cb, &io, st, zc9, sc2, tab, arena, segs.data(), 1, 0, 1);
     return 0;
 }
+
+// ---- the generic MQ encoder (RESET / TERMALL) the CUDA kernel k_t1_mq_gen runs, compiled for the host ----
+#include "../../j2k_b200/csrc/t1_mq_gen.cuh"
+extern "C" int mqgen_host(const uint8_t* sym, const uint32_t* pass_nsym, int npasses, int cblksty, const uint32_t* mq, uint8_t* out, int cap,
+                          int32_t* rate, int32_t* total) {
+    return j2k::mqgen::encode_block(sym, pass_nsym, npasses, cblksty, mq, out, cap, rate, total);
+}

@@ -73,6 +73,30 @@ def t1_encode(smag, orient, maxmag=None):
                 rates=[rates[i] for i in range(k)], nmsedec=[nms[i] for i in range(k)])
 
 
+def t1_encode_sty(smag, orient, cblksty, maxmag=None, trace=False):
+    """the generic encoder loop (RESET 2 / TERMALL 4): like t1_encode; with trace also the (ctx << 1 | d) symbols and per-pass counts"""
+    smag = np.ascontiguousarray(smag, dtype=np.uint32)
+    h, w = smag.shape
+    if maxmag is None:
+        maxmag = int((smag & 0x7FFFFFFF).max()) if smag.size else 0
+    out = np.empty(w * h * 8 + 64, dtype=np.uint8)
+    numbps = C.c_int(0)
+    npasses = C.c_int(0)
+    rates = (C.c_int * 128)()
+    nms = (C.c_int * 128)()
+    tr = np.zeros(w * h * 64 + 64, dtype=np.uint8) if trace else None
+    pn = (C.c_uint32 * 128)()
+    n = lib().orc_t1_encode_cblk_sty(_p(smag), w, h, orient, C.c_uint32(maxmag), cblksty, _p(out), out.size, C.byref(numbps),
+                                     C.byref(npasses), rates, nms, _p(tr) if trace else None, tr.size if trace else 0, pn)
+    assert n >= 0, n
+    k = npasses.value
+    r = dict(data=out[:n].tobytes(), numbps=numbps.value, npasses=k, rates=[rates[i] for i in range(k)], nmsedec=[nms[i] for i in range(k)])
+    if trace:
+        r["pass_nsym"] = [pn[i] for i in range(k)]
+        r["symbols"] = tr[:sum(r["pass_nsym"])].copy()
+    return r
+
+
 def t1_decode(data, w, h, orient, numbps, npasses):
     out = np.zeros((h, w), dtype=np.int32)
     buf = np.frombuffer(data, dtype=np.uint8)
