@@ -28,7 +28,7 @@ class Params(C.Structure):
                 ("max_comp_size", C.c_uint32), ("max_cs_size", C.c_uint64),
                 ("rates", C.c_double * 16), ("compat", C.c_uint32), ("device", C.c_int32),
                 ("tile_first", C.c_uint32), ("tile_count", C.c_uint32),
-                ("reserved", C.c_uint32 * 4)]
+                ("cblksty", C.c_uint32), ("reserved", C.c_uint32 * 3)]
 
 
 class Info(C.Structure):

@@ -87,15 +87,18 @@ J2K_MQG_HD inline int encode_block(const uint8_t* sym, const uint32_t* pass_nsym
                 q.renorm();
             }
         }
-        int correction = 3;
+        const int correction = 3;
         if (cblksty & STY_TERMALL) {                             // t1.cpp:1618-1647
             q.flush();
-            correction = 1;
             q.a = 0x8000u; q.c = 0; q.ct = 12; --q.bp;           // opj_mqc_restart_init_enc
             if (q.get(q.bp) == 0xff) q.ct = 13;
         }
-        rate[p] = q.numbytes();
-        if (rate[p] > 0) rate[p] += correction;
+        // The reference adds the correction only when numbytes > 0 (t1.cpp:1649-1651).  After a termination that loses a segment
+        // that is exactly one byte long (last byte at index 0: "no bytes" and "one byte" both give numbytes 0): the pass gets
+        // length 0 and neither the reference's decoder nor OpenJPEG can read the block (tests/test_t1_mq_generic.py).  A
+        // terminated pass always owns the bytes up to and including the one the restart stepped back to.
+        rate[p] = (cblksty & STY_TERMALL) ? q.bp + 1 : q.numbytes();
+        if (!(cblksty & STY_TERMALL) && rate[p] > 0) rate[p] += correction;
         if (cblksty & STY_RESET) reset_states(st);               // t1.cpp:1654-1656
     }
     q.flush();                                                   // t1.cpp:1659-1663 (neither PTERM nor LAZY)

@@ -36,6 +36,7 @@ const char* check_params(const ::j2kcuda_params& p) {
         return "code-block size must be a power of two between 4 and 1024 with at most 4096 samples";
     if (p.numlayers > 100) return "too many layers";
     if (p.prog_order > J2KCUDA_CPRL) return "unknown progression order";
+    if (p.cblksty & ~0x06u) return "code-block styles other than RESET (0x02) and TERMALL (0x04) are not supported by the encoder";
     return nullptr;
 }
 
@@ -123,7 +124,7 @@ void setup_coding_params(const ::j2kcuda_params& p, CodingParams& cp) {
         t.csty = csty & 1;
         t.numres = numres;
         t.cblkw = floorlog2((uint32_t)cbw); t.cblkh = floorlog2((uint32_t)cbh);
-        t.cblksty = 0;
+        t.cblksty = (int)p.cblksty;
         t.qmfbid = irreversible ? 0 : 1;
         t.qntsty = irreversible ? 2 : 0;
         t.numgbits = 2;
@@ -274,12 +275,25 @@ static uint64_t encode_packet(const CodingParams& cp, EncTile& t, const PacketId
             if (!layer.numpasses) continue;
             if (!cblk.numpasses) { cblk.numlenbits = 3; t.imsb[ti].encode(bio, k, 999); }
             putnumpasses(bio, (uint32_t)layer.numpasses);
-            // cblksty == 0: one codeword segment per layer contribution
-            int len = layer.len;
-            int increment = std::max(0, floorlog2((uint32_t)len) + 1 - (cblk.numlenbits + floorlog2((uint32_t)layer.numpasses)));
-            putcommacode(bio, increment);
-            cblk.numlenbits += increment;
-            bio.write((uint32_t)len, cblk.numlenbits + floorlog2((uint32_t)layer.numpasses));
+            if (!(cp.comps[compno].cblksty & 4)) {
+                // no pass of the contribution is terminated (cblksty 0 or RESET): one codeword segment, one length
+                int len = layer.len;
+                int increment = std::max(0, floorlog2((uint32_t)len) + 1 - (cblk.numlenbits + floorlog2((uint32_t)layer.numpasses)));
+                putcommacode(bio, increment);
+                cblk.numlenbits += increment;
+                bio.write((uint32_t)len, cblk.numlenbits + floorlog2((uint32_t)layer.numpasses));
+            } else {
+                // TERMALL: every pass ends a codeword segment, so every pass has a length of its own (t2.cpp:738-790); Lblock
+                // grows by the largest increment any of them needs
+                const int p0 = cblk.numpasses, p1 = cblk.numpasses + layer.numpasses;
+                auto passlen = [&](int p) { return cblk.rates[p] - (p ? cblk.rates[p - 1] : 0); };
+                int increment = 0;
+                for (int pno = p0; pno < p1; ++pno)
+                    increment = std::max(increment, floorlog2((uint32_t)passlen(pno)) + 1 - cblk.numlenbits);   // one pass per segment: floorlog2(1) = 0
+                putcommacode(bio, increment);
+                cblk.numlenbits += increment;
+                for (int pno = p0; pno < p1; ++pno) bio.write((uint32_t)passlen(pno), cblk.numlenbits);
+            }
         }
     }
     bio.flush();

@@ -526,7 +526,7 @@ int orc_t1_encode_cblk(const uint32_t* smag, int w, int h, int orient, uint32_t 
 int orc_t1_encode_cblk_sty(const uint32_t* smag, int w, int h, int orient, uint32_t maxmag, int cblksty,
                            uint8_t* out, int cap, int* numbps, int* npasses, int* rates, int* nmsedec,
                            uint8_t* trace, int trace_cap, uint32_t* pass_nsym) {
-    if (cblksty & ~0x06) return -2;
+    if (cblksty & ~0x106) return -2;
     nm_init();
     t1state_t s;
     if (t1s_init(&s, w, h)) return -1;
@@ -555,6 +555,10 @@ int orc_t1_encode_cblk_sty(const uint32_t* smag, int w, int h, int orient, uint3
         if (++passtype == 3) { passtype = 0; bpno--; }
         rates[passno] = mqe_numbytes(&q);
         if (rates[passno] > 0) rates[passno] += correction;
+        /* REFERENCE DEFECT kept only on request (cblksty bit 0x100): after a termination, numbytes == 0 also means "one byte,
+         * at index 0", and the reference then reports length 0 for the pass; its own decoder cannot read such a block.  The
+         * correct length of a terminated pass is everything up to and including the byte the restart stepped back to. */
+        else if ((cblksty & 0x04) && !(cblksty & 0x100)) rates[passno] = (int)(q.bp - q.start) + 1;
         if (cblksty & 0x02) mq_reset(q.st, q.mps);              /* t1.cpp:1654-1656 */
     }
     g_trace = NULL;

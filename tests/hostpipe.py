@@ -54,7 +54,8 @@ def encode(planes, prec, params, sgnd=0):
             r = dict(data=b"", numbps=0, npasses=0, rates=[], nmsedec=[])
         else:
             q, mx = orc.quantize(blk, qmfbid=0 if irreversible else 1, bandconst=bandconst)
-            r = orc.t1_encode(q, orient, mx)
+            sty = int(params.cblksty)
+            r = orc.t1_encode_sty(q, orient, sty, mx) if sty else orc.t1_encode(q, orient, mx)
         stepsize = np.array([stepsize_bits], dtype=np.int32).view(np.float32)[0]
         mctn = 1.0
         if params.mct and comp < 3 and int(params.ncomp) >= 3:
