@@ -131,7 +131,7 @@ void launch_t1_context(const T1Block* d_blocks, int nblocks, uint8_t* sym_arena,
                        T1Result* results, cudaStream_t st);
 void launch_t1_mq(const T1Block* d_blocks, int nblocks, const uint8_t* sym_arena,
                   const uint32_t* pass_nsym, uint8_t* out_arena, T1Result* results,
-                  int lanes_per_warp, uint32_t* d_order, int max_long, cudaStream_t st);
+                  int lanes_per_warp, uint32_t* d_order, int max_long, cudaStream_t st, int cblksty = 0);
 // (d_order: scratch of nblocks + 2 words, or null: filled with the block indices by decreasing symbol count;
 //  the blocks at least half as long as the longest, at most max_long of them, get a warp each)
 // gather the kept bytes of every block into one contiguous buffer (offsets = exclusive scan of

@@ -174,6 +174,7 @@ static int setup_encoder(j2kcuda_encoder* e) {
             b.sym_off = (uint32_t)sym_units; b.sym_cap = (uint32_t)cap;
             sym_units += cap / 16;
             size_t ocap = 64 + area * ((size_t)b.max_planes + 2) / 4;
+            if (cp.comps[cb.comp].cblksty & 4) ocap += 3 * 3 * ((size_t)b.max_planes + 1);      // TERMALL: a flush (up to 3 bytes) after every pass
             ocap = (ocap + 15) & ~(size_t)15;
             b.out_off = (uint32_t)out_off; b.out_cap = (uint32_t)ocap;
             out_off += ocap;
@@ -513,7 +514,7 @@ int j2kcuda_encoder_run(j2kcuda_encoder* e) { return j2k::guarded([&]() -> int {
     CK(cudaEventRecord(e->ev[2], st));
     launch_t1_context(e->d_blocks, e->nblocks, e->d_sym, e->d_pass_nsym, e->d_results, st); ++launches;
     CK(cudaEventRecord(e->ev[3], st));
-    launch_t1_mq(e->d_blocks, e->nblocks, e->d_sym, e->d_pass_nsym, e->d_out, e->d_results, e->mq_lanes, e->d_mq_order, e->mq_nlong, st); launches += 2;
+    launch_t1_mq(e->d_blocks, e->nblocks, e->d_sym, e->d_pass_nsym, e->d_out, e->d_results, e->mq_lanes, e->d_mq_order, e->mq_nlong, st, e->cp.comps[0].cblksty); launches += e->cp.comps[0].cblksty ? 1 : 2;
     CK(cudaEventRecord(e->ev[4], st));
     launch_t1_compact(e->d_blocks, e->nblocks, e->d_out, e->d_results, e->d_offsets, e->d_packed, st); launches += 2;
     if (e->nblocks) {

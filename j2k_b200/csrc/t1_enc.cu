@@ -19,6 +19,7 @@
 // top to bottom inside a column.
 #include "device.h"
 #include "t1_tables.cuh"
+#include "t1_mq_gen.cuh"
 #include <cstdlib>
 
 namespace j2k {
@@ -599,6 +600,28 @@ k_t1_mq(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __restr
     res.total = lastrate;
 }
 
+// ---- MQ coder for the code-block styles RESET / TERMALL (row a21): the reference's generic loop, t1_mq_gen.cuh ------------
+// One block per thread, no ordering: streams with these styles are rare, and the routine is the byte-pointer form that
+// reproduces the reference's termination arithmetic rather than the branch-free form above.
+__global__ void __launch_bounds__(MQ_THREADS)
+k_t1_mq_gen(const T1Block* __restrict__ blocks, int nblocks, const T1Tables* __restrict__ tab, const uint8_t* __restrict__ sym_arena,
+            const uint32_t* __restrict__ pass_nsym, uint8_t* __restrict__ out_arena, T1Result* __restrict__ results, int cblksty) {
+    __shared__ uint32_t s_mq[96];
+    if (threadIdx.x < 94) s_mq[threadIdx.x] = tab->mq[threadIdx.x];
+    __syncthreads();
+    const int bi = blockIdx.x * MQ_THREADS + threadIdx.x;
+    if (bi >= nblocks) return;
+    T1Result& res = results[bi];
+    const int npasses = res.npasses;
+    if (npasses == 0 || res.status != 0) { res.total = 0; return; }
+    const T1Block blk = blocks[bi];
+    int32_t total = 0;
+    const int rc = mqgen::encode_block(sym_arena + (size_t)blk.sym_off * 16, pass_nsym + (size_t)bi * T1_MAX_PASSES, npasses, cblksty, s_mq,
+                                       out_arena + blk.out_off, (int)blk.out_cap, res.rate, &total);
+    res.total = total;
+    if (rc) res.status = rc;
+}
+
 // ---- compaction: exclusive scan of the kept byte counts, then one warp copies one block --------
 __global__ void __launch_bounds__(1024) k_t1_scan(const T1Result* __restrict__ results, int nblocks, uint32_t* __restrict__ offsets) {
     __shared__ uint32_t s_warp[32];
@@ -656,8 +679,13 @@ void launch_t1_context(const T1Block* d_blocks, int nblocks, uint8_t* sym_arena,
 }
 
 void launch_t1_mq(const T1Block* d_blocks, int nblocks, const uint8_t* sym_arena, const uint32_t* pass_nsym,
-                  uint8_t* out_arena, T1Result* results, int lanes_per_warp, uint32_t* d_order, int max_long, cudaStream_t st) {
+                  uint8_t* out_arena, T1Result* results, int lanes_per_warp, uint32_t* d_order, int max_long, cudaStream_t st, int cblksty) {
     if (nblocks <= 0) return;
+    if (cblksty) {                                   // RESET / TERMALL: the generic coder (the caller has refused every other bit)
+        k_t1_mq_gen<<<(nblocks + MQ_THREADS - 1) / MQ_THREADS, MQ_THREADS, 0, st>>>(d_blocks, nblocks, t1_tables_device(), sym_arena, pass_nsym,
+                                                                                  out_arena, results, cblksty);
+        return;
+    }
     if (lanes_per_warp < 1) lanes_per_warp = 1;
     if (lanes_per_warp > 32) lanes_per_warp = 32;
     if (max_long < 0 || !d_order) max_long = 0;
