@@ -1,6 +1,7 @@
 // MQ encoder of one code-block for the code-block styles that only touch the arithmetic coder: RESET (contexts back to their
-// initial states after every pass) and TERMALL (the coder is flushed and restarted after every pass, so every pass is a
-// codeword segment of its own).  This is the reference's GENERIC loop (ext/grok/src/lib/openjp2/t1.cpp:1537-1673), not the
+// initial states after every pass), TERMALL (the coder is flushed and restarted after every pass, so every pass is a
+// codeword segment of its own), PTERM (predictable termination at the end) and SEGSYM (the symbols 1, 0, 1, 0 in the UNI
+// context after every clean-up pass: they are coded here, the modelling kernel does not know about them).  This is the reference's GENERIC loop (ext/grok/src/lib/openjp2/t1.cpp:1537-1673), not the
 // optimised one k_t1_mq follows (t1_opt.cpp:659-739): a pass's rate is numbytes + 3, or + 1 when the pass was terminated, and
 // only when numbytes > 0; the restart steps back over the last byte (mqc.cpp:521-532) and drops a trailing 0xFF; the final
 // flush comes on top of the last pass's own.  The context modelling is unchanged, so the input is the same (context, decision)
@@ -22,7 +23,7 @@
 namespace j2k {
 namespace mqgen {
 
-enum { STY_RESET = 0x02, STY_TERMALL = 0x04, STY_SUPPORTED = STY_RESET | STY_TERMALL };
+enum { STY_RESET = 0x02, STY_TERMALL = 0x04, STY_PTERM = 0x10, STY_SEGSYM = 0x20, STY_SUPPORTED = STY_RESET | STY_TERMALL | STY_PTERM | STY_SEGSYM };
 
 struct Enc {
     uint32_t a, c, ct;
@@ -59,6 +60,22 @@ J2K_MQG_HD inline void reset_states(uint8_t* st) {               // t1.cpp:1578-
     st[CTX_UNI] = 46 * 2; st[CTX_AGG] = 3 * 2; st[CTX_ZC] = 4 * 2;
 }
 
+J2K_MQG_HD inline void code(Enc& q, uint8_t* st, const uint32_t* mq, uint32_t ctx, uint32_t d) {
+    const uint32_t e = mq[st[ctx]], qe = e & 0xffffu;
+    q.a -= qe;
+    if ((st[ctx] & 1u) == d) {                                   // mqc.cpp:271-283 (codemps)
+        if ((q.a & 0x8000u) == 0) {
+            if (q.a < qe) q.a = qe; else q.c += qe;
+            st[ctx] = (uint8_t)((e >> 16) & 0xffu);
+            q.renorm();
+        } else q.c += qe;
+    } else {                                                     // mqc.cpp:285-297 (codelps)
+        if (q.a < qe) q.c += qe; else q.a = qe;
+        st[ctx] = (uint8_t)(e >> 24);
+        q.renorm();
+    }
+}
+
 // sym: (ctx << 1) | d per decision; pass_nsym[p] decisions belong to pass p.  mq: T1Tables::mq (qe | next-if-MPS << 16 |
 // next-if-LPS << 24, indices state * 2 + mps).  rate[p] = cumulative bytes after pass p as the reference reports them.
 // Returns 0, or 2 when `cap` bytes do not hold the block.
@@ -71,22 +88,9 @@ J2K_MQG_HD inline int encode_block(const uint8_t* sym, const uint32_t* pass_nsym
     uint32_t pos = 0;
     for (int p = 0; p < npasses; ++p) {
         const uint32_t end = pos + pass_nsym[p];
-        for (; pos < end; ++pos) {
-            const uint32_t s = sym[pos], ctx = (s >> 1) & 31u, d = s & 1u;
-            const uint32_t e = mq[st[ctx]], qe = e & 0xffffu;
-            q.a -= qe;
-            if ((st[ctx] & 1u) == d) {                           // mqc.cpp:271-283 (codemps)
-                if ((q.a & 0x8000u) == 0) {
-                    if (q.a < qe) q.a = qe; else q.c += qe;
-                    st[ctx] = (uint8_t)((e >> 16) & 0xffu);
-                    q.renorm();
-                } else q.c += qe;
-            } else {                                             // mqc.cpp:285-297 (codelps)
-                if (q.a < qe) q.c += qe; else q.a = qe;
-                st[ctx] = (uint8_t)(e >> 24);
-                q.renorm();
-            }
-        }
+        for (; pos < end; ++pos) { const uint32_t sb = sym[pos]; code(q, st, mq, (sb >> 1) & 31u, sb & 1u); }
+        if ((cblksty & STY_SEGSYM) && p % 3 == 0)                // the first pass and every third after it are clean-up passes
+            for (uint32_t i = 1; i < 5; ++i) code(q, st, mq, CTX_UNI, i & 1u);   // t1.cpp:1598-1600, mqc.cpp:550-558: 1, 0, 1, 0
         const int correction = 3;
         if (cblksty & STY_TERMALL) {                             // t1.cpp:1618-1647
             q.flush();
@@ -101,7 +105,11 @@ J2K_MQG_HD inline int encode_block(const uint8_t* sym, const uint32_t* pass_nsym
         if (!(cblksty & STY_TERMALL) && rate[p] > 0) rate[p] += correction;
         if (cblksty & STY_RESET) reset_states(st);               // t1.cpp:1654-1656
     }
-    q.flush();                                                   // t1.cpp:1659-1663 (neither PTERM nor LAZY)
+    if (cblksty & STY_PTERM) {                                   // predictable termination: opj_mqc_erterm_enc, mqc.cpp:534-548
+        int k = (int)(11 - q.ct + 1);
+        while (k > 0) { q.c <<= q.ct; q.ct = 0; q.byteout(); k -= (int)q.ct; }
+        if (q.get(q.bp) != 0xff) q.byteout();
+    } else q.flush();                                            // t1.cpp:1659-1663
     const int nbytes = q.numbytes();
     if (q.overflow || nbytes > cap) { *total = 0; return 2; }
     int last = 0;

@@ -526,7 +526,7 @@ int orc_t1_encode_cblk(const uint32_t* smag, int w, int h, int orient, uint32_t 
 int orc_t1_encode_cblk_sty(const uint32_t* smag, int w, int h, int orient, uint32_t maxmag, int cblksty,
                            uint8_t* out, int cap, int* numbps, int* npasses, int* rates, int* nmsedec,
                            uint8_t* trace, int trace_cap, uint32_t* pass_nsym) {
-    if (cblksty & ~0x106) return -2;
+    if (cblksty & ~0x136) return -2;                       /* RESET 0x02, TERMALL 0x04, PTERM 0x10, SEGSYM 0x20 (+ 0x100, see below) */
     nm_init();
     t1state_t s;
     if (t1s_init(&s, w, h)) return -1;
@@ -543,7 +543,14 @@ int orc_t1_encode_cblk_sty(const uint32_t* smag, int w, int h, int orient, uint3
         int nm = 0, before = g_trace_n, correction = 3;
         if (passtype == 0) enc_sigpass(&s, &q, smag, bpno, orient, &nm);
         else if (passtype == 1) enc_refpass(&s, &q, smag, bpno, &nm);
-        else enc_clnpass(&s, &q, smag, bpno, orient, &nm);
+        else {
+            enc_clnpass(&s, &q, smag, bpno, orient, &nm);
+            if (cblksty & 0x20) {                               /* SEGSYM: 1, 0, 1, 0 in the UNI context after every clean-up pass */
+                uint8_t* keep = g_trace; g_trace = NULL;        /* (t1.cpp:1598-1600, mqc.cpp:550-558); not part of the modelling trace */
+                for (int i = 1; i < 5; ++i) mqe_encode(&q, CTX_UNI, (uint32_t)(i % 2));
+                g_trace = keep;
+            }
+        }
         nmsedec[passno] = nm;
         if (pass_nsym) pass_nsym[passno] = (uint32_t)(g_trace_n - before);
         if (cblksty & 0x04) {                                   /* t1.cpp:1618-1647 */
@@ -562,7 +569,11 @@ int orc_t1_encode_cblk_sty(const uint32_t* smag, int w, int h, int orient, uint3
         if (cblksty & 0x02) mq_reset(q.st, q.mps);              /* t1.cpp:1654-1656 */
     }
     g_trace = NULL;
-    mqe_flush(&q);                                              /* t1.cpp:1659-1663 (no PTERM, no LAZY) */
+    if (cblksty & 0x10) {                                       /* PTERM: opj_mqc_erterm_enc, mqc.cpp:534-548 */
+        int k = (int)(11 - q.ct + 1);
+        while (k > 0) { q.c <<= q.ct; q.ct = 0; mqe_byteout(&q); k -= (int)q.ct; }
+        if (*q.bp != 0xff) mqe_byteout(&q);
+    } else mqe_flush(&q);                                       /* t1.cpp:1659-1663 */
     *npasses = passno;
     int total = mqe_numbytes(&q);
     const uint8_t* data = buf + 1;
