@@ -82,9 +82,9 @@ typedef struct j2kcuda_params {
      * header, no EOC); j2kcuda_join_tile_streams() puts the fragments of all ranks together.
      * tile_count == 0: the whole frame, a complete codestream. */
     uint32_t tile_first, tile_count;
-    /* Code-block style (Scod / SPcod byte, j2k.h:77-82; opj_cparameters_t::mode).  The encoder supports RESET (0x02) and
-     * TERMALL (0x04) and their combination: the styles that only touch the arithmetic coder (t1.cpp:1537-1673, row a21);
-     * other bits are refused.  The decoder reads all six.  0 = none (what the plug-in writes). */
+    /* Code-block style (Scod / SPcod byte, j2k.h:77-82; opj_cparameters_t::mode).  The encoder supports RESET (0x02), TERMALL
+     * (0x04), SEGSYM (0x20) and their combinations: styles the arithmetic-coder stage can do alone (t1.cpp:1537-1673, row
+     * a21); LAZY, VSC and PTERM are refused.  The decoder reads all six.  0 = none (what the plug-in writes). */
     uint32_t cblksty;
     uint32_t reserved[3];
 } j2kcuda_params;

@@ -1,7 +1,9 @@
 // MQ encoder of one code-block for the code-block styles that only touch the arithmetic coder: RESET (contexts back to their
 // initial states after every pass), TERMALL (the coder is flushed and restarted after every pass, so every pass is a
-// codeword segment of its own), PTERM (predictable termination at the end) and SEGSYM (the symbols 1, 0, 1, 0 in the UNI
-// context after every clean-up pass: they are coded here, the modelling kernel does not know about them).  This is the reference's GENERIC loop (ext/grok/src/lib/openjp2/t1.cpp:1537-1673), not the
+// codeword segment of its own) and SEGSYM (the symbols 1, 0, 1, 0 in the UNI context after every clean-up pass: they are coded
+// here, the modelling kernel does not know about them).  PTERM is left out on purpose: the reference's predictable termination
+// (mqc.cpp:534-548 with the byte count of t1.cpp:1667-1670) writes small blocks that neither its own decoder nor OpenJPEG reads
+// back (64 x 64 image, six resolutions), and there is nothing to pin a corrected version against.  This is the reference's GENERIC loop (ext/grok/src/lib/openjp2/t1.cpp:1537-1673), not the
 // optimised one k_t1_mq follows (t1_opt.cpp:659-739): a pass's rate is numbytes + 3, or + 1 when the pass was terminated, and
 // only when numbytes > 0; the restart steps back over the last byte (mqc.cpp:521-532) and drops a trailing 0xFF; the final
 // flush comes on top of the last pass's own.  The context modelling is unchanged, so the input is the same (context, decision)
@@ -23,7 +25,7 @@
 namespace j2k {
 namespace mqgen {
 
-enum { STY_RESET = 0x02, STY_TERMALL = 0x04, STY_PTERM = 0x10, STY_SEGSYM = 0x20, STY_SUPPORTED = STY_RESET | STY_TERMALL | STY_PTERM | STY_SEGSYM };
+enum { STY_RESET = 0x02, STY_TERMALL = 0x04, STY_SEGSYM = 0x20, STY_SUPPORTED = STY_RESET | STY_TERMALL | STY_SEGSYM };
 
 struct Enc {
     uint32_t a, c, ct;
@@ -105,11 +107,7 @@ J2K_MQG_HD inline int encode_block(const uint8_t* sym, const uint32_t* pass_nsym
         if (!(cblksty & STY_TERMALL) && rate[p] > 0) rate[p] += correction;
         if (cblksty & STY_RESET) reset_states(st);               // t1.cpp:1654-1656
     }
-    if (cblksty & STY_PTERM) {                                   // predictable termination: opj_mqc_erterm_enc, mqc.cpp:534-548
-        int k = (int)(11 - q.ct + 1);
-        while (k > 0) { q.c <<= q.ct; q.ct = 0; q.byteout(); k -= (int)q.ct; }
-        if (q.get(q.bp) != 0xff) q.byteout();
-    } else q.flush();                                            // t1.cpp:1659-1663
+    q.flush();                                                   // t1.cpp:1659-1663 (neither PTERM nor LAZY)
     const int nbytes = q.numbytes();
     if (q.overflow || nbytes > cap) { *total = 0; return 2; }
     int last = 0;

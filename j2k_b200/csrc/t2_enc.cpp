@@ -36,7 +36,7 @@ const char* check_params(const ::j2kcuda_params& p) {
         return "code-block size must be a power of two between 4 and 1024 with at most 4096 samples";
     if (p.numlayers > 100) return "too many layers";
     if (p.prog_order > J2KCUDA_CPRL) return "unknown progression order";
-    if (p.cblksty & ~0x36u) return "the encoder supports the code-block styles RESET (0x02), TERMALL (0x04), PTERM (0x10) and SEGSYM (0x20); LAZY and VSC are refused";
+    if (p.cblksty & ~0x26u) return "the encoder supports the code-block styles RESET (0x02), TERMALL (0x04) and SEGSYM (0x20); LAZY, VSC and PTERM are refused";
     return nullptr;
 }
 

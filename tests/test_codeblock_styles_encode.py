@@ -1,5 +1,6 @@
-"""Row a21: ENCODING with the code-block styles RESET (0x02), TERMALL (0x04), PTERM (0x10) and SEGSYM (0x20) -- the four the
-arithmetic-coder stage can do alone (LAZY needs raw sign bits, VSC changes the context modelling: refused).
+"""Row a21: ENCODING with the code-block styles RESET (0x02), TERMALL (0x04) and SEGSYM (0x20) -- styles the arithmetic-coder
+stage can do alone.  Refused: LAZY (needs raw sign bits), VSC (changes the context modelling), PTERM (the reference's own PTERM
+streams of small images decode neither in its decoder nor in OpenJPEG, and there is nothing to pin a corrected one against).
 
 CPU: oracle stages + the product's Tier-2 writer (tests/hostpipe.py) against the compiled reference.  RESET streams are the
 reference's byte for byte.  TERMALL streams are the reference's byte for byte wherever the reference's own stream can be decoded;
@@ -44,7 +45,7 @@ def lossless(kw):
     return not kw.get("irreversible") and (not r or r[-1] == 0)
 
 
-STYLES = [0x02, 0x04, 0x06, 0x10, 0x20, 0x36]      # RESET 2, TERMALL 4, PTERM 0x10, SEGSYM 0x20
+STYLES = [0x02, 0x04, 0x06, 0x20, 0x26]      # RESET 2, TERMALL 4, SEGSYM 0x20
 
 
 @pytest.mark.parametrize("case", range(len(CASES)))
@@ -71,7 +72,7 @@ def test_host_pipeline_against_the_reference(sty, case):
         assert np.array_equal(im.reshape(h, w, nc), img)
 
 
-@pytest.mark.parametrize("sty", [4, 6, 0x36])
+@pytest.mark.parametrize("sty", [2, 4, 6, 0x20, 0x26])
 def test_small_images_whose_deep_levels_hit_the_reference_defect(sty):
     """64 x 64 with six resolutions: 2 x 2 code-blocks at the top of the pyramid, terminated passes of one byte"""
     if not refgrok.available():
@@ -85,7 +86,7 @@ def test_small_images_whose_deep_levels_hit_the_reference_defect(sty):
 
 
 def test_other_style_bits_are_refused():
-    for sty in (1, 8, 9, 7, 0x40):
+    for sty in (1, 8, 0x10, 7, 0x40):
         p = L.default_params(width=64, height=64, ncomp=1, prec=8, cblksty=sty)
         assert L.lib().j2kcuda_t2_block_count(L.C.byref(p) if hasattr(L, "C") else __import__("ctypes").byref(p)) < 0
         assert "RESET" in L.last_error()

@@ -74,6 +74,8 @@ def test_oracle_generic_loop_equals_the_reference(sty):
         if sty & 4:
             assert all(b["terms"])
         c = orc.t1_encode_sty(smag, orient, sty, mx)
+        if sty & 0x10:
+            continue                      # PTERM: the restatement is pinned, nothing more (the reference's own blocks do not all decode)
         assert decodes_back(c, coeff, orient, sty)
         if c["rates"] != b["rates"]:
             # t1.cpp:1649-1651: numbytes == 0 after a termination is "one byte", the reference says "none"
@@ -84,7 +86,7 @@ def test_oracle_generic_loop_equals_the_reference(sty):
     assert sty not in (4, 6) or defects > 0     # the small blocks of these samples do hit it
 
 
-@pytest.mark.parametrize("sty", STYLES)
+@pytest.mark.parametrize("sty", [s for s in STYLES if not s & 0x10])         # the device core has no PTERM (see t1_mq_gen.cuh)
 def test_host_compiled_device_core_equals_the_oracle_and_decodes_in_the_reference(core, sty):
     lib, tab = core
     have_ref = refgrok.available()
