@@ -36,6 +36,7 @@ static int roundtrip(double seconds, unsigned seed0) {
         const bool lossy = rng() % 2;
         for (unsigned k = 0; k < p.numlayers; ++k) p.rates[k] = lossy ? (k + 1 == p.numlayers && (rng() & 1) ? 0.0 : 40.0 / (k + 1) + (rng() % 10)) : 0.0;
         p.compat = rng() % 3;
+        { static const uint32_t stys[6] = {0, 0, 0x02, 0x04, 0x20, 0x26}; p.cblksty = stys[rng() % 6]; }   // RESET, TERMALL, SEGSYM
         const int nb = j2kcuda_t2_block_count(&p);
         if (nb < 0) { ++refused; continue; }
         if (nb == 0 || nb > 20000) continue;
@@ -70,6 +71,11 @@ static int roundtrip(double seconds, unsigned seed0) {
                     if (b.numbps != res[k].numbps || b.npasses < 1 || b.npasses > res[k].npasses || b.len != rates[k][b.npasses - 1]) {
                         printf("block %d: numbps %d/%d passes %d/%d len %d\n", k, b.numbps, res[k].numbps, b.npasses, res[k].npasses, b.len); return 2;
                     }
+                    if (p.cblksty & 4) {                                      // TERMALL: one codeword segment per pass, each with the pass's length
+                        if ((int)b.segs.size() != b.npasses) { printf("block %d: %zu segments for %d terminated passes\n", k, b.segs.size(), b.npasses); return 2; }
+                        for (int q = 0; q < b.npasses; ++q)
+                            if (b.segs[q].numpasses != 1 || b.segs[q].len != rates[k][q] - (q ? rates[k][q - 1] : 0)) { printf("block %d: segment %d differs\n", k, q); return 2; }
+                    } else if (b.segs.size() != 1) { printf("block %d: %zu segments without TERMALL\n", k, b.segs.size()); return 2; }
                     size_t pos = 0;
                     for (auto& c : b.chunks) { if (memcmp(out + c.first, data[k].data() + pos, c.second)) { printf("block %d: bytes differ\n", k); return 2; } pos += c.second; }
                     if ((int)pos != b.len) { printf("block %d: chunks do not add up\n", k); return 2; }
