@@ -302,6 +302,9 @@ static uint64_t encode_packet(const CodingParams& cp, EncTile& t, const PacketId
         if (out) { out->push_back(0xff); out->push_back(0x92); }
         nbytes += 2;
     }
+    // bodies: the encoder's packed arena holds the blocks of a band back to back in this very order, so the contributions of
+    // neighbouring blocks are usually one run of memory: copied as runs, not block by block
+    const uint8_t* run = nullptr; size_t runlen = 0;
     for (int b = 0; b < res.numbands; ++b) {
         if (res.bands[b].r.w() <= 0 || res.bands[b].r.h() <= 0) continue;
         const PrecGeo& prc = res.bands[b].precs[precno];
@@ -309,11 +312,16 @@ static uint64_t encode_packet(const CodingParams& cp, EncTile& t, const PacketId
             EncBlock& cblk = t.blocks[prc.first_cblk + k];
             const EncLayer& layer = cblk.layers[layno];
             if (!layer.numpasses) continue;
-            if (out) out->insert(out->end(), cblk.data + layer.data_off, cblk.data + layer.data_off + layer.len);
+            if (out && layer.len > 0) {
+                const uint8_t* src = cblk.data + layer.data_off;
+                if (run && src == run + runlen) runlen += (size_t)layer.len;
+                else { if (runlen) out->insert(out->end(), run, run + runlen); run = src; runlen = (size_t)layer.len; }
+            }
             cblk.numpasses += layer.numpasses;
             nbytes += (uint64_t)layer.len;
         }
     }
+    if (out && runlen) out->insert(out->end(), run, run + runlen);
     return nbytes;
 }
 

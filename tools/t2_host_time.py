@@ -12,13 +12,18 @@ n = len(geo)
 rng = np.random.default_rng(0)
 results = (L.BlockResult * n)()
 keep = []
+# the code bytes of all blocks back to back in block order, as the encoder's packed arena holds them after the D2H copy
+all_rates = [np.cumsum(rng.integers(20, 80, size=28)).astype(np.int32) for _ in range(n)]
+arena = rng.integers(0, 255, size=int(sum(int(r[-1]) for r in all_rates)) + 64, dtype=np.uint8)
+off = 0
 for i in range(n):
     npasses = 28
-    rates = np.cumsum(rng.integers(20, 80, size=npasses)).astype(np.int32)
-    data = rng.integers(0, 255, size=int(rates[-1]) + 1, dtype=np.uint8)
+    rates = all_rates[i]
+    data = arena[off:off + int(rates[-1])]
+    off += int(rates[-1])
     dist = np.cumsum(rng.random(npasses) * 1e6)[::1].copy()
     keep.append((rates, data, dist))
-    results[i].data = data.ctypes.data_as(C.POINTER(C.c_uint8))
+    results[i].data = C.cast(arena.ctypes.data + (off - int(rates[-1])), C.POINTER(C.c_uint8))
     results[i].numbps = 10; results[i].npasses = npasses
     results[i].rates = rates.ctypes.data_as(C.POINTER(C.c_int32))
     results[i].dist = dist.ctypes.data_as(C.POINTER(C.c_double))
