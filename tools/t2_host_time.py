@@ -4,10 +4,11 @@ import numpy as np
 sys.path.insert(0, os.path.join(os.path.dirname(__file__), ".."))
 sys.path.insert(0, os.path.join(os.path.dirname(__file__), "..", "tests"))
 from j2k_b200 import _lib as L
-import hostpipe
 lib = L.lib()
 p = L.default_params(width=4096, height=2160, ncomp=4, prec=16, mct=1, numresolution=6)
-geo = hostpipe.block_list(p)
+nblk = lib.j2kcuda_t2_block_count(C.byref(p))          # the library's own block table (no oracle in tools/)
+geo = np.zeros((nblk, 12), dtype=np.int32)
+assert lib.j2kcuda_t2_block_geometry(C.byref(p), geo.ctypes.data_as(C.c_void_p), nblk) == nblk
 n = len(geo)
 rng = np.random.default_rng(0)
 results = (L.BlockResult * n)()
